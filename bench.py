@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py -- SSPS parent-set scoring / MH hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json metric point): synthetic DBN from the simulate_data.jl restatement,
+V=100 nodes, T=8, M=4 series (n=28 lagged rows), regression_deg 1, lambda-prop-std 3.0, large-indeg 15,
+thinning 1; `--chains` independent chains PER GPU (weak scaling), one step = `--sweeps` sweeps of every
+chain (one sweep = V lambda moves + V scored parent-set proposals; only the latter are counted).
+
+  value  scored parent-set proposals / s, whole job, state resident in HBM, CUDA-event timed
+  e2e    same metric through the host-buffer API: per step set_data (H2D) + init_chains + sweeps +
+         PSRF + edge posterior (D2H)
+  roofline   FP64: algorithmic flops F(k) = k^3/3 + 2k^2 + 2k per scored proposal over the MH
+             kernel's device time, against the DFMA peak measured on this GPU by the library
+  cpu_baseline   the reference-faithful oracle (QR scorer + [i;S] cache), all host cores, bounded sample
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "scored parent-set proposals/sec/box at V=100"
+UNIT = "proposals/s"
+
+
+def make_workload(V, T, M, seed=20200701):
+    from ssps_b200.simulate import simulate
+    ds = simulate(V, T, M, seed=seed)
+    xm, xp = ds.lagged()
+    return ds, xm, xp
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def run_reference(args, rank, world):
+    """CPU arm: the reference-faithful oracle (QR least squares on every [i;S] cache miss), one chain per
+    host core.  The Julia reference itself cannot run here (no julia binary)."""
+    if rank != 0:
+        return
+    from oracle import oracle as orc
+    ds, xm, xp = make_workload(args.V, args.T, args.M)
+    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std)
+    cores = os.cpu_count() or 1
+    chains = cores
+    # size one step for ~3 s of CPU work
+    t, nprop, _ = P.run_chains_mt(chains, cores, 20, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    sweeps = max(20, int(20 * 3.0 / max(t, 1e-3)))
+    for w in range(args.warmup):
+        P.run_chains_mt(chains, cores, sweeps, seed=2 + w, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    tot_t, tot_p = 0.0, 0
+    for k in range(args.steps):
+        t, nprop, _ = P.run_chains_mt(chains, cores, sweeps, seed=100 + k, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE,
+                                      want_counts=False)
+        tot_t += t
+        tot_p += nprop
+    value = tot_p / tot_t
+    sample = "%d chains x %d sweeps per step on %d threads (oracle QR scorer + [i;S] lml cache)" % (chains, sweeps, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "simulate_data.jl restatement V=%d T=%d M=%d (n=%d), deg 1" % (args.V, args.T, args.M, P.n),
+                   "chains": chains, "sweeps_per_step": sweeps},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference runtime (Julia 1.6 + Gen 0.4.5) unavailable on this box; CPU port of its algorithm, an upper bound on its speed",
+    }))
+
+
+def cpu_baseline(args):
+    from oracle import oracle as orc
+    ds, xm, xp = make_workload(args.V, args.T, args.M)
+    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std)
+    cores = os.cpu_count() or 1
+    t, nprop, _ = P.run_chains_mt(cores, cores, 20, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    sweeps = max(20, int(20 * 12.0 / max(t, 1e-3)))
+    t, nprop, _ = P.run_chains_mt(cores, cores, sweeps, seed=3, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    return {"value": nprop / t, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d chains x %d sweeps (%.1f s) of the same workload, oracle QR scorer + [i;S] lml cache, one chain per thread"
+                      % (cores, sweeps, t)}
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from ssps_b200 import Sampler
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    ds, xm, xp = make_workload(args.V, args.T, args.M)
+    V, C, S = args.V, args.chains, args.sweeps
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    smp = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=S)
+    smp.set_stream(stream.cuda_stream)
+    smp.set_data(xm, xp, ds.prior_graph)
+    smp.generate(C, seed=args.seed, chain_id_offset=rank * C)
+    fp64_peak = smp.measure_fp64_peak()
+    sums = torch.zeros(smp.psrf_sums_len(), dtype=torch.float64, device=dev)
+
+    def step():
+        smp.update_loop(S)
+
+    def psrf_exchange():
+        # the path's one real exchange: PSRF sufficient statistics summed over ranks (NCCL over NVLink)
+        smp.psrf_sums_device(0.5, sums.data_ptr())
+        if world > 1:
+            dist.all_reduce(sums)
+        return smp.psrf_finish(None, device_ptr=sums.data_ptr())[0]
+
+    for _ in range(args.warmup):
+        step()
+    psrf_exchange()
+    st0 = smp.stats()
+    barrier()
+    clk = ClockSampler(local_rank)
+    clk.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    max_psrf = psrf_exchange()
+    ev1.record(stream)
+    barrier()
+    clk.stop_flag = True
+    ms = ev0.elapsed_time(ev1)
+    st1 = smp.stats()
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    agg = torch.tensor([st1.n_proposals - st0.n_proposals, st1.n_accepted - st0.n_accepted], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(agg)
+    ms = float(t.item())
+    proposals = float(agg[0].item())
+    value = proposals / (ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (mh_sweeps_kernel), this rank ----
+    k_ms = st1.kernel_ms - st0.kernel_ms
+    launches = st1.mh_launches - st0.mh_launches
+    flops = st1.algorithmic_flops - st0.algorithmic_flops
+    gbytes = st1.algorithmic_bytes - st0.algorithmic_bytes
+    nprop_local = st1.n_proposals - st0.n_proposals
+    ach = flops / (k_ms * 1e-3) / 1e12
+    roofline = {"bound": "fp64", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": None,
+                "kernel": "mh_sweeps_kernel<PhiloxSource>", "launches": launches, "avg_launch_ms": k_ms / max(launches, 1),
+                "kernel_share_of_step": k_ms / ms,
+                "peak_source": "DFMA peak measured on this GPU by ssps_measure_fp64_peak (MEASURED_PEAKS.json has no FP64 figure)",
+                "mean_k": (st1.sum_k - st0.sum_k) / max(nprop_local, 1),
+                "algorithmic_flops_per_proposal": flops / max(nprop_local, 1),
+                "gather_GBps": gbytes / (k_ms * 1e-3) / 1e9,
+                "kernel_proposals_per_s": nprop_local / (k_ms * 1e-3)}
+
+    # ---- e2e: host buffers in, posterior out, every step ----
+    e2e = None
+    if not args.no_e2e:
+        xm_h, xp_h, pr_h = np.asfortranarray(xm), np.asfortranarray(xp), np.asfortranarray(ds.prior_graph)
+        h2d = xm_h.nbytes + xp_h.nbytes + pr_h.nbytes
+        d2h = V * V * 8 * 2 + V * 8 + 8
+
+        def e2e_step(seed):
+            s2 = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=S // 4)
+            s2.set_stream(stream.cuda_stream)
+            s2.set_data(xm_h, xp_h, pr_h)
+            s2.generate(C, seed=seed, chain_id_offset=rank * C)
+            s2.update_loop(S)
+            mx, _ = s2.psrf(0.5)
+            probs, _, _, _ = s2.edge_posterior(0.5)
+            s2.close()
+            return probs
+
+        for w in range(min(args.warmup, 2)):
+            e2e_step(1000 + w)
+        barrier()
+        t0 = time.perf_counter()
+        n_e2e = max(1, min(args.steps, 3))
+        for k in range(n_e2e):
+            e2e_step(2000 + k)
+        barrier()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * C * V * S * n_e2e / float(tt.item()), "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "steps": n_e2e,
+               "what": "per step: ssps_create + set_data(H2D) + init_chains + %d sweeps + psrf + edge_posterior(D2H), wall clock" % S}
+
+    smp.close()
+    if rank != 0:
+        return
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "simulate_data.jl restatement V=%d T=%d M=%d (n=%d), regression_deg 1, lambda_prop_std %g, large_indeg %g, thinning 1"
+                               % (V, args.T, args.M, smp.n, args.lambda_prop_std, args.large_indeg),
+                   "chains_per_gpu": C, "sweeps_per_step": S, "parallelism": "chains sharded over %d GPU(s), no data-path collective; one PSRF all-reduce per timed region" % world,
+                   "l2": "chain state + tallies (%.0f MB) exceed L2; G/R tables (%.0f kB) are cache-resident by design" % (2 * C * V * V * 4 / 1e6, 2 * V * V * 8 / 1e3)},
+        "roofline": roofline, "e2e": e2e, "gpu_launches": int(st1.kernel_launches - st0.kernel_launches),
+        "clocks": clk.summary(), "max_edge_psrf": max_psrf,
+        "accept_rate": float(agg[1].item()) / max(proposals, 1.0),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(args)
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
+    ap.add_argument("--V", type=int, default=100)
+    ap.add_argument("--T", type=int, default=8)
+    ap.add_argument("--M", type=int, default=4)
+    ap.add_argument("--chains", type=int, default=4096, help="chains per GPU")
+    ap.add_argument("--sweeps", type=int, default=200, help="sweeps per step")
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--large-indeg", type=float, default=15.0)
+    ap.add_argument("--lambda-prop-std", type=float, default=3.0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return 0
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl")
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,188 @@
+/*
+ * ssps.h -- C ABI of libssps_b200.so: the B200-native replacement for the ONE hot path of
+ * gitter-lab/ssps: scoring proposed parent sets (per-node DBN marginal likelihood + edge prior)
+ * inside the Metropolis-Hastings sweep, batched over chains x vertices x proposals.
+ *
+ * What each entry point replaces in the reference (paths relative to the reference checkout):
+ *
+ *   ssps_set_data / ssps_set_timeseries
+ *        combine_X / standardize_X / vectorize_X        SSPS/src/dbn_preprocess.jl:70-108
+ *        compute_B_col / construct_B (regression_deg 1) SSPS/src/dbn_distributions.jl:168-194
+ *        prob_param_i, lambda_min                       SSPS/src/SSPS.jl:164-169
+ *   ssps_score
+ *        log_marg_lik / compute_lml / safe_solve        SSPS/src/dbn_distributions.jl:201-264
+ *        logpdf(::ConfParentPrior, ...)                 SSPS/src/dbn_distributions.jl:96-153
+ *        logpdf(::CPDMarginal, ...)                     SSPS/src/dbn_distributions.jl:303-306
+ *   ssps_init_chains
+ *        Gen.generate(vertex_lambda_dbn_model, ...)     SSPS/src/mcmc_inference.jl:40,
+ *                                                       SSPS/src/dbn_models.jl:66-99,
+ *        random(::ConfParentPrior, ...)                 SSPS/src/dbn_distributions.jl:75-89
+ *        recover_state! (resume)                        SSPS/src/SSPS.jl:24-43,187-196
+ *   ssps_run / ssps_replay
+ *        mcmc_inference loop                            SSPS/src/mcmc_inference.jl:58-79
+ *        vertex_lambda_update_loop / multithread_...    SSPS/src/state_updates.jl:35-93
+ *        smart_proposal / smart_involution              SSPS/src/dbn_proposals.jl:60-130
+ *        lambda_vec_proposal                            SSPS/src/dbn_proposals.jl:244-248
+ *        Gen.mh acceptance (Gen 0.4.5, not in tree)     call sites state_updates.jl:44-47
+ *   ssps_edge_counts / ssps_edge_posterior
+ *        increment_counts! / update_results_summary     SSPS/src/state_updates.jl:120-140,240-249
+ *        evaluate_summary                               scripts/postprocess_samples.jl:183-191
+ *   ssps_changepoints_*
+ *        update_results_storediff                       SSPS/src/state_updates.jl:161-227
+ *   ssps_psrf / ssps_psrf_sums / ssps_psrf_finish
+ *        evaluate_convergence / compute_psrf_neff       scripts/postprocess_samples.jl:99-180
+ *
+ * Conventions: all indices 0-based (the 1-based <-> 0-based shift lives in the language shim);
+ * matrices column-major; the caller owns every buffer passed in or out (inputs are copied to the
+ * device inside the call); every function returns 0 or a negative ssps_status and leaves a
+ * message for ssps_last_error() (thread-local).  No exceptions cross this boundary.  A handle
+ * is bound to one CUDA device; calls on one handle are not re-entrant.
+ * There is NO CPU fallback: without a CUDA device every call fails with SSPS_ERR_CUDA.
+ */
+#ifndef SSPS_H
+#define SSPS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSPS_ABI_VERSION 1
+
+typedef enum {
+    SSPS_OK = 0,
+    SSPS_ERR_INVALID = -1,      /* bad argument / call order */
+    SSPS_ERR_CUDA = -2,         /* CUDA runtime error (message has the cudaError string) */
+    SSPS_ERR_UNSUPPORTED = -3,  /* e.g. regression_deg != 1, --proposal uniform */
+    SSPS_ERR_NOMEM = -4,
+    SSPS_ERR_INDEGREE = -5,     /* a proposed parent set exceeded max_indegree scratch */
+    SSPS_ERR_UNAVAILABLE = -6   /* e.g. PSRF requested before any snapshot exists */
+} ssps_status;
+
+typedef struct ssps_handle ssps_handle;
+
+typedef struct {
+    int32_t struct_size;      /* = sizeof(ssps_config) */
+    int32_t device;           /* CUDA ordinal; -1 = current device */
+    int32_t regression_deg;   /* --regression-deg; only 1 is implemented */
+    int32_t max_indegree;     /* scratch capacity for |S'| (0 = min(V, 64)); sets may still hold up to V parents
+                                 only if <= this bound */
+    double  large_indeg;      /* --large-indeg   (SSPS.jl:64-67)  */
+    double  lambda_max;       /* --lambda-max    (SSPS.jl:68-70)  */
+    double  lambda_prop_std;  /* --lambda-prop-std (SSPS.jl:75-78) */
+    int32_t psrf_grid;        /* snapshot the per-chain tallies every this many recorded samples
+                                 (0 = default 250, <0 = never) */
+    int32_t record_changepoints; /* 1: keep the reference's change-point log (small runs only) */
+    int32_t collect_khist;    /* 1: histogram of proposed |S'| (diagnostics; slower) */
+    int32_t reserved;
+} ssps_config;
+
+typedef struct {
+    int64_t sweeps_done;        /* per chain */
+    int64_t samples_recorded;   /* per chain, the reference's results["n"] */
+    int64_t n_proposals;        /* parent-set proposals scored, all chains (lambda moves not counted) */
+    int64_t n_accepted;         /* parent-set proposals accepted */
+    int64_t n_lambda_accepted;
+    int64_t sum_k;              /* sum over proposals of |S'| */
+    double  algorithmic_flops;  /* sum over proposals of F(|S'|) = k^3/3 + 2k^2 + 2k */
+    double  algorithmic_bytes;  /* sum over proposals of 8 (k(k+1)/2 + k) */
+    double  kernel_ms;          /* device time of the MH kernel launches (CUDA events) */
+    int64_t kernel_launches;    /* all kernels launched by this handle */
+    int64_t mh_launches;        /* MH sweep kernel launches */
+} ssps_run_stats;
+
+const char* ssps_last_error(void);
+int  ssps_abi_version(void);
+
+int  ssps_create(const ssps_config* cfg, ssps_handle** out);
+void ssps_destroy(ssps_handle* h);
+/* Launch all work on this CUDA stream (a cudaStream_t); NULL = the legacy default stream. */
+int  ssps_set_stream(ssps_handle* h, void* cuda_stream);
+
+/* K1: raw lagged design -> standardised Z, Y -> G = Z'Z, R = Z'Y (fp64) + prior tables.
+ * Xminus, Xplus: n x V column-major, RAW (only Xplus is pre-standardised by the reference,
+ * SSPS.jl:156; Xminus is standardised per column inside compute_B_col).
+ * prior: V x V column-major, entry [parent j + V * child i], values <= 0 mean "no confidence". */
+int  ssps_set_data(ssps_handle* h, const double* Xminus, const double* Xplus, int32_t n, int32_t V,
+                   const double* prior);
+/* Same, from M concatenated time series (rows of series m are contiguous, already sorted by
+ * timestep): X is (sum series_len) x V column-major; lagging is done on the device. */
+int  ssps_set_timeseries(ssps_handle* h, const double* X, const int32_t* series_len, int32_t n_series,
+                         int32_t V, const double* prior);
+/* test hooks: copy back what K1 built (any pointer may be NULL) */
+int  ssps_get_design(ssps_handle* h, double* Z, double* Y);
+int  ssps_get_gram(ssps_handle* h, double* G, double* R, double* yty);
+int  ssps_get_derived(ssps_handle* h, double* lambda_min, double* prob_param /* V */);
+int  ssps_get_dims(ssps_handle* h, int32_t* n, int32_t* V, int32_t* n_chains);
+
+/* K2: score n_sets (child, S) pairs.  S sorted ascending, unique.  lambda may be NULL when
+ * logprior_out is NULL.  min_pivot_out (nullable) = smallest accepted Schur pivot / G_jj, a
+ * conditioning diagnostic (inf for k = 0). */
+int  ssps_score(ssps_handle* h, int32_t n_sets, const int32_t* child, const int32_t* set_offsets,
+                const int32_t* set_members, const double* lambda, double* lml_out, double* logprior_out,
+                double* min_pivot_out);
+
+/* Chains.  chain ids are chain_id_offset .. chain_id_offset + n_chains - 1 (they key the Philox
+ * streams, so ranks of a multi-GPU job pass disjoint offsets).  init_offsets (n_chains*V + 1),
+ * init_members, init_lambda (n_chains*V, [chain*V + vertex]) are all-or-nothing; NULL => draw
+ * the initial state from the model (sweep-0 Philox blocks). */
+int  ssps_init_chains(ssps_handle* h, int32_t n_chains, uint64_t seed, uint32_t chain_id_offset,
+                      const int32_t* init_offsets, const int32_t* init_members, const double* init_lambda);
+
+/* K3: run up to n_sweeps sweeps per chain (one sweep = V lambda moves + V parent-set moves),
+ * recording every `thinning`-th state; stops early once timeout_s (<= 0: none) is exceeded,
+ * checked between kernel launches. */
+int  ssps_run(ssps_handle* h, int64_t n_sweeps, double timeout_s, int32_t thinning, int64_t* sweeps_done);
+/* Same sweeps, but driven by a recorded stream: draws is n_sweeps x n_chains x V x 6 doubles
+ * (z_lambda, u_lambda, u_action, u_add, u_rem, u_accept), host memory. */
+int  ssps_replay(ssps_handle* h, int64_t n_sweeps, const double* draws, int32_t thinning);
+
+/* Current state of one chain: indeg[V], members (concatenated sorted parent lists, capacity cap,
+ * *n_members = total), lambda[V], lml[V] (any may be NULL). */
+int  ssps_get_state(ssps_handle* h, int32_t chain, int32_t* indeg, int32_t* members, int64_t cap,
+                    int64_t* n_members, double* lambda, double* lml);
+
+/* Tallies over recorded samples 1..n of all local chains: counts[child*V + parent]. */
+int  ssps_edge_counts(ssps_handle* h, double* counts_child_major, int64_t* n_samples, int32_t* n_chains);
+/* Per-chain tallies: counts[(chain*V + child)*V + parent], uint32. */
+int  ssps_chain_edge_counts(ssps_handle* h, uint32_t* counts);
+/* evaluate_summary: pooled post-burn-in edge frequencies probs[child*V + parent];
+ * burnin_used/n_used report the (snapshot-aligned) indices actually used. */
+int  ssps_edge_posterior(ssps_handle* h, double burnin, double* probs_child_major, double* lambda_mean,
+                         int64_t* burnin_used, int64_t* n_used);
+
+/* K4: split-chain PSRF of every edge indicator and every lambda_i (postprocess_samples.jl:99-180).
+ * ssps_psrf_sums writes the additive sufficient statistics of the LOCAL chains:
+ *   sums[0 .. 3*V*V)        per edge: sum_h m_h, sum_h m_h^2, sum_h var_h   (h = half-chains)
+ *   sums[3*V*V .. +3*V)     per lambda_i: same three
+ *   sums[.. +2]             number of half-chains H, and H * n (n = half length), so that n = tail[1] / tail[0]
+ *                           survives a SUM all-reduce
+ * so that ranks can add them (ncclAllReduce / torch.distributed.all_reduce) before
+ * ssps_psrf_finish.  on_device != 0: `sums` is a DEVICE pointer on this handle's device. */
+int64_t ssps_psrf_sums_len(int32_t V);
+int  ssps_psrf_sums(ssps_handle* h, double burnin, double* sums, int32_t on_device);
+int  ssps_psrf_finish(ssps_handle* h, const double* sums, int32_t on_device, double* max_edge_psrf,
+                      double* edge_psrf_child_major /* V*V, nullable, NaN where W == 0 */,
+                      double* lambda_psrf /* V, nullable */);
+/* local convenience = sums + finish */
+int  ssps_psrf(ssps_handle* h, double burnin, double* max_edge_psrf, double* edge_psrf_child_major);
+
+/* Change-point log of one chain (needs record_changepoints = 1): two-call protocol.
+ * Parent events: (sample n, child, parent, value 0|1), ordered by (child, parent, n).
+ * Lambda events: (sample n, child, value), ordered by (child, n).  Index 0 = initial state. */
+int  ssps_changepoints_size(ssps_handle* h, int32_t chain, int64_t* n_parent_events, int64_t* n_lambda_events);
+int  ssps_changepoints_get(ssps_handle* h, int32_t chain,
+                           int64_t* pe_n, int32_t* pe_child, int32_t* pe_parent, int32_t* pe_value,
+                           int64_t* le_n, int32_t* le_child, double* le_value);
+
+int  ssps_get_stats(ssps_handle* h, ssps_run_stats* out);
+int  ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len);
+/* Device-side microbenchmark used by bench.py for the FP64 roofline denominator: dependent-free
+ * DFMA streams on every SM; returns achieved TFLOP/s. */
+int  ssps_measure_fp64_peak(ssps_handle* h, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,1068 @@
+// ssps_capi.cu -- host side of libssps_b200.so: the C ABI declared in include/ssps.h.
+//
+// One handle = one CUDA device.  Every entry point validates its arguments, launches the sm_100a
+// kernels of ssps_kernels.cuh on the handle's stream and returns 0 or a negative ssps_status
+// (message through ssps_last_error()).  There is NO CPU implementation of any scoring or
+// sampling step in this file: without a CUDA device every call fails with SSPS_ERR_CUDA.
+//
+// Host-side arithmetic is limited to bookkeeping: lag row maps (combine_X,
+// SSPS/src/dbn_preprocess.jl:70-87), grouping equal prior confidences (so that the device
+// normaliser visits each distinct value once), snapshot scheduling and turning the device's
+// per-launch toggle log into the reference's change-point lists
+// (update_results_storediff, SSPS/src/state_updates.jl:161-227).
+#include "../../include/ssps.h"
+#include "ssps_kernels.cuh"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <unordered_map>
+#include <utility>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(SSPS_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+#define CKS(expr)                    \
+    do {                             \
+        int s_ = (expr);             \
+        if (s_ != SSPS_OK) return s_; \
+    } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+        return *this;
+    }
+    ~DevBuf() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    cudaError_t alloc(size_t count) {
+        release();
+        if (count == 0) count = 1;
+        cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+        if (e == cudaSuccess) n = count; else p = nullptr;
+        return e;
+    }
+    size_t bytes() const { return n * sizeof(T); }
+};
+
+struct Snapshot {
+    int64_t n = 0;                 // recorded samples per chain at the time of the copy
+    DevBuf<uint32_t> counts;       // [chain][child][parent]
+    DevBuf<double> lam_sum, lam_sq;
+};
+
+struct ParentEvent { int64_t n; int32_t child, parent, value; };
+struct LambdaEvent { int64_t n; int32_t child; double value; };
+
+inline int div_up(size_t a, size_t b) { return (int)((a + b - 1) / b); }
+
+}  // namespace
+
+struct ssps_handle {
+    ssps_config cfg{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int sm_count = 0;
+
+    // ---- data (K1) ----
+    int n = 0, V = 0;
+    bool has_data = false;
+    DevBuf<double> Xminus, Xplus, Z, Y, G, R, yty, conf, omc, prob_param, mvP, mvLogP, logint, grp_omc, grp_mult;
+    DevBuf<int> grp_off;
+    double lambda_min = 0.0;
+    SspsDev dev{};
+
+    // ---- chains (K3) ----
+    int n_chains = 0, nch_pad = 0;
+    uint64_t seed = 0;
+    uint32_t chain_offset = 0;
+    int kcap = 0;                   // scratch capacity in rows (max |S'|)
+    int thinning = 0;               // fixed by the first ssps_run / ssps_replay
+    int64_t sweeps_done = 0, samples_recorded = 0;
+    DevBuf<int> k;
+    DevBuf<double> lambda, lam_sum, lam_sq;
+    DevBuf<uint32_t> slots, counts;
+    ChainState st{};
+    int mh_grid = 0;
+    size_t mh_smem = 0;
+    DevBuf<double> arena_d;
+    DevBuf<uint16_t> arena_t;
+    DevBuf<int> task_counter;
+    DevBuf<unsigned long long> stats, khist;
+
+    // ---- snapshots for split-PSRF / burn-in (K4) ----
+    int64_t snap_grid = 0;          // in recorded samples; 0 = disabled
+    size_t snap_budget_bytes = 0;
+    std::vector<Snapshot> snaps;    // ascending n, all multiples of snap_grid
+    DevBuf<double> sums_scratch, psrf_scratch;
+    DevBuf<unsigned long long> max_bits;
+
+    // ---- change-point log (small runs) ----
+    int pev_cap = 0, lev_cap = 0;
+    DevBuf<uint32_t> pev;
+    DevBuf<int> pev_n, lev_n;
+    DevBuf<double> lev_val;
+    DevBuf<uint16_t> lev_idx;
+    std::vector<std::vector<ParentEvent>> cp_parent;   // per chain
+    std::vector<std::vector<LambdaEvent>> cp_lambda;   // per chain
+    std::vector<uint8_t> cp_present;                   // [chain][child][parent] at the last recorded sample
+    std::vector<double> cp_lambda_last;                // [chain][child]
+
+    // ---- stats ----
+    double kernel_ms = 0.0;
+    int64_t kernel_launches = 0, mh_launches = 0;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pool;
+
+    ~ssps_handle() {
+        for (auto& e : ev_pool) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    }
+};
+
+namespace {
+
+int bind(ssps_handle* h) {
+    if (!h) return fail(SSPS_ERR_INVALID, "null handle");
+    CK(cudaSetDevice(h->device));
+    return SSPS_OK;
+}
+
+template <class T>
+int upload(ssps_handle* h, DevBuf<T>& dst, const T* src, size_t count) {
+    CK(dst.alloc(count));
+    if (count) CK(cudaMemcpyAsync(dst.p, src, count * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+    return SSPS_OK;
+}
+
+template <class T>
+int download(ssps_handle* h, T* dst, const T* src, size_t count) {
+    if (count) CK(cudaMemcpyAsync(dst, src, count * sizeof(T), cudaMemcpyDeviceToHost, h->stream));
+    return SSPS_OK;
+}
+
+int launch_ok(ssps_handle* h, const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(SSPS_ERR_CUDA, "%s launch: %s", what, cudaGetErrorString(e));
+    ++h->kernel_launches;
+    return SSPS_OK;
+}
+
+// Z, Y, G, R, yty, prior tables, move tables from raw Xminus / Xplus already on the device.
+int finish_data(ssps_handle* h, const double* prior_host) {
+    const int n = h->n, V = h->V;
+    const size_t nv = (size_t)n * V, vv = (size_t)V * V;
+    cudaStream_t s = h->stream;
+    CK(h->Z.alloc(nv)); CK(h->Y.alloc(nv)); CK(h->G.alloc(vv)); CK(h->R.alloc(vv)); CK(h->yty.alloc(V));
+    CK(h->conf.alloc(vv)); CK(h->omc.alloc(vv)); CK(h->prob_param.alloc(V));
+    CK(h->mvP.alloc((size_t)V * (V + 1) * 3)); CK(h->mvLogP.alloc((size_t)V * (V + 1) * 3)); CK(h->logint.alloc(V + 2));
+
+    standardize_kernel<<<div_up(V, 128), 128, 0, s>>>(h->Xminus.p, n, V, h->Z.p);   // quirk Q4
+    CKS(launch_ok(h, "standardize(Xminus)"));
+    standardize_kernel<<<div_up(V, 128), 128, 0, s>>>(h->Xplus.p, n, V, h->Y.p);    // SSPS.jl:156
+    CKS(launch_ok(h, "standardize(Xplus)"));
+    dim3 grid(div_up(V, GRAM_TILE), div_up(V, GRAM_TILE));
+    gram_kernel<<<grid, GRAM_TILE * 8, 0, s>>>(h->Z.p, h->Z.p, n, V, V, h->G.p);
+    CKS(launch_ok(h, "gram(G)"));
+    gram_kernel<<<grid, GRAM_TILE * 8, 0, s>>>(h->Z.p, h->Y.p, n, V, V, h->R.p);
+    CKS(launch_ok(h, "gram(R)"));
+    yty_kernel<<<div_up(V, 128), 128, 0, s>>>(h->Y.p, n, V, h->yty.p);
+    CKS(launch_ok(h, "yty"));
+
+    DevBuf<double> prior_dev;
+    CKS(upload(h, prior_dev, prior_host, vv));
+    prior_kernel<<<div_up(vv, 256), 256, 0, s>>>(prior_dev.p, vv, h->conf.p, h->omc.p);
+    CKS(launch_ok(h, "prior"));
+    prob_param_kernel<<<div_up(V, 128), 128, 0, s>>>(h->conf.p, V, h->prob_param.p);
+    CKS(launch_ok(h, "prob_param"));
+    move_table_kernel<<<div_up((size_t)V * (V + 1) + 2, 256), 256, 0, s>>>(h->prob_param.p, V, h->mvP.p, h->mvLogP.p, h->logint.p);
+    CKS(launch_ok(h, "move_table"));
+
+    // distinct (1 - c) values per child, order of first appearance (bookkeeping only: the
+    // normaliser sum_j log1p(exp(-lambda (1 - c_ji))) then costs one exp/log1p per distinct value)
+    std::vector<int> goff(V + 1, 0);
+    std::vector<double> gomc, gmult;
+    gomc.reserve(4 * (size_t)V); gmult.reserve(4 * (size_t)V);
+    for (int i = 0; i < V; ++i) {
+        goff[i] = (int)gomc.size();
+        std::unordered_map<uint64_t, int> seen;
+        for (int j = 0; j < V; ++j) {
+            const double pr = prior_host[(size_t)j + (size_t)V * i];
+            const double o = 1.0 - (pr > 0.0 ? pr : 0.0);
+            uint64_t bits;
+            memcpy(&bits, &o, sizeof bits);
+            auto it = seen.find(bits);
+            if (it == seen.end()) {
+                seen.emplace(bits, (int)gomc.size());
+                gomc.push_back(o); gmult.push_back(1.0);
+            } else {
+                gmult[it->second] += 1.0;
+            }
+        }
+    }
+    goff[V] = (int)gomc.size();
+    CKS(upload(h, h->grp_off, goff.data(), goff.size()));
+    CKS(upload(h, h->grp_omc, gomc.data(), gomc.size()));
+    CKS(upload(h, h->grp_mult, gmult.data(), gmult.size()));
+    CK(cudaStreamSynchronize(s));   // host vectors go out of scope
+
+    // SSPS.jl:169  lambda_min = log(max(V / large_indeg - 1, exp(0.5)))
+    h->lambda_min = log(fmax((double)V / h->cfg.large_indeg - 1.0, exp(0.5)));
+    SspsDev& d = h->dev;
+    d.n = n; d.V = V; d.dn = (double)n; d.shrink = (double)n / ((double)n + 1.0); d.log1pn = log(1.0 + (double)n);
+    d.lambda_min = h->lambda_min; d.lambda_max = h->cfg.lambda_max; d.sigma = h->cfg.lambda_prop_std;
+    d.G = h->G.p; d.R = h->R.p; d.yty = h->yty.p; d.omc = h->omc.p; d.conf = h->conf.p;
+    d.grp_off = h->grp_off.p; d.grp_omc = h->grp_omc.p; d.grp_mult = h->grp_mult.p;
+    d.mvP = h->mvP.p; d.mvLogP = h->mvLogP.p; d.logint = h->logint.p;
+    h->has_data = true;
+    // any chains belong to the previous data set
+    h->n_chains = 0;
+    h->snaps.clear();
+    return SSPS_OK;
+}
+
+int check_dims(int n, int V) {
+    if (n < 2) return fail(SSPS_ERR_INVALID, "need at least 2 lagged rows, got n=%d", n);
+    if (V < 1 || V > 65535) return fail(SSPS_ERR_INVALID, "V=%d outside 1..65535 (parent ids are 16-bit on the device)", V);
+    return SSPS_OK;
+}
+
+}  // namespace
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+extern "C" {
+
+const char* ssps_last_error(void) { return g_err.c_str(); }
+int ssps_abi_version(void) { return SSPS_ABI_VERSION; }
+
+int ssps_create(const ssps_config* cfg, ssps_handle** out) {
+    if (!cfg || !out) return fail(SSPS_ERR_INVALID, "ssps_create: null argument");
+    if (cfg->struct_size != (int32_t)sizeof(ssps_config))
+        return fail(SSPS_ERR_INVALID, "ssps_config.struct_size=%d, library expects %d", cfg->struct_size, (int)sizeof(ssps_config));
+    if (cfg->regression_deg != 1)
+        return fail(SSPS_ERR_UNSUPPORTED, "regression_deg=%d: only the degree-1 design is implemented (DESIGN.md, out of scope)",
+                    cfg->regression_deg);
+    if (!(cfg->large_indeg > 0.0) || !(cfg->lambda_prop_std > 0.0))
+        return fail(SSPS_ERR_INVALID, "large_indeg and lambda_prop_std must be positive");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (ndev < 1) return fail(SSPS_ERR_CUDA, "no CUDA device (libssps_b200 has no CPU path)");
+    int dev = cfg->device;
+    if (dev < 0) CK(cudaGetDevice(&dev));
+    if (dev >= ndev) return fail(SSPS_ERR_INVALID, "device %d out of range (%d visible)", dev, ndev);
+    ssps_handle* h = new (std::nothrow) ssps_handle();
+    if (!h) return fail(SSPS_ERR_NOMEM, "out of host memory");
+    h->cfg = *cfg;
+    h->device = dev;
+    cudaError_t e = cudaSetDevice(dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) { delete h; return fail(SSPS_ERR_CUDA, "device %d: %s", dev, cudaGetErrorString(e)); }
+    double lmin = log(fmax(1.0, exp(0.5)));
+    if (!(cfg->lambda_max > lmin)) { delete h; return fail(SSPS_ERR_INVALID, "lambda_max=%g must exceed 0.5", cfg->lambda_max); }
+    *out = h;
+    return SSPS_OK;
+}
+
+void ssps_destroy(ssps_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    delete h;
+}
+
+int ssps_set_stream(ssps_handle* h, void* cuda_stream) {
+    CKS(bind(h));
+    CK(cudaStreamSynchronize(h->stream));
+    h->stream = (cudaStream_t)cuda_stream;
+    return SSPS_OK;
+}
+
+int ssps_set_data(ssps_handle* h, const double* Xminus, const double* Xplus, int32_t n, int32_t V, const double* prior) {
+    CKS(bind(h));
+    if (!Xminus || !Xplus || !prior) return fail(SSPS_ERR_INVALID, "ssps_set_data: null argument");
+    CKS(check_dims(n, V));
+    h->n = n; h->V = V; h->has_data = false;
+    CKS(upload(h, h->Xminus, Xminus, (size_t)n * V));
+    CKS(upload(h, h->Xplus, Xplus, (size_t)n * V));
+    return finish_data(h, prior);
+}
+
+int ssps_set_timeseries(ssps_handle* h, const double* X, const int32_t* series_len, int32_t n_series, int32_t V,
+                        const double* prior) {
+    CKS(bind(h));
+    if (!X || !series_len || !prior || n_series < 1) return fail(SSPS_ERR_INVALID, "ssps_set_timeseries: bad argument");
+    // combine_X (dbn_preprocess.jl:70-87): Xminus = rows 1..T-1, Xplus = rows 2..T of every series
+    std::vector<int> row_map;
+    int total = 0;
+    for (int m = 0; m < n_series; ++m) {
+        if (series_len[m] < 1) return fail(SSPS_ERR_INVALID, "series %d has length %d", m, series_len[m]);
+        for (int t = 0; t + 1 < series_len[m]; ++t) row_map.push_back(total + t);
+        total += series_len[m];
+    }
+    const int n = (int)row_map.size();
+    CKS(check_dims(n, V));
+    h->n = n; h->V = V; h->has_data = false;
+    DevBuf<double> Xd;
+    DevBuf<int> map_d;
+    CKS(upload(h, Xd, X, (size_t)total * V));
+    CKS(upload(h, map_d, row_map.data(), row_map.size()));
+    CK(h->Xminus.alloc((size_t)n * V)); CK(h->Xplus.alloc((size_t)n * V));
+    lag_gather_kernel<<<div_up((size_t)n * V, 256), 256, 0, h->stream>>>(Xd.p, total, V, map_d.p, n, h->Xminus.p, h->Xplus.p);
+    CKS(launch_ok(h, "lag_gather"));
+    CK(cudaStreamSynchronize(h->stream));
+    return finish_data(h, prior);
+}
+
+int ssps_get_design(ssps_handle* h, double* Z, double* Y) {
+    CKS(bind(h));
+    if (!h->has_data) return fail(SSPS_ERR_INVALID, "no data set");
+    const size_t nv = (size_t)h->n * h->V;
+    if (Z) CKS(download(h, Z, h->Z.p, nv));
+    if (Y) CKS(download(h, Y, h->Y.p, nv));
+    CK(cudaStreamSynchronize(h->stream));
+    return SSPS_OK;
+}
+
+int ssps_get_gram(ssps_handle* h, double* G, double* R, double* yty) {
+    CKS(bind(h));
+    if (!h->has_data) return fail(SSPS_ERR_INVALID, "no data set");
+    const size_t vv = (size_t)h->V * h->V;
+    if (G) CKS(download(h, G, h->G.p, vv));
+    if (R) CKS(download(h, R, h->R.p, vv));
+    if (yty) CKS(download(h, yty, h->yty.p, (size_t)h->V));
+    CK(cudaStreamSynchronize(h->stream));
+    return SSPS_OK;
+}
+
+int ssps_get_derived(ssps_handle* h, double* lambda_min, double* prob_param) {
+    CKS(bind(h));
+    if (!h->has_data) return fail(SSPS_ERR_INVALID, "no data set");
+    if (lambda_min) *lambda_min = h->lambda_min;
+    if (prob_param) CKS(download(h, prob_param, h->prob_param.p, (size_t)h->V));
+    CK(cudaStreamSynchronize(h->stream));
+    return SSPS_OK;
+}
+
+int ssps_get_dims(ssps_handle* h, int32_t* n, int32_t* V, int32_t* n_chains) {
+    if (!h) return fail(SSPS_ERR_INVALID, "null handle");
+    if (n) *n = h->n;
+    if (V) *V = h->V;
+    if (n_chains) *n_chains = h->n_chains;
+    return SSPS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2
+// ------------------------------------------------------------------------------------------------
+int ssps_score(ssps_handle* h, int32_t n_sets, const int32_t* child, const int32_t* set_offsets,
+               const int32_t* set_members, const double* lambda, double* lml_out, double* logprior_out,
+               double* min_pivot_out) {
+    CKS(bind(h));
+    if (!h->has_data) return fail(SSPS_ERR_INVALID, "ssps_score before ssps_set_data");
+    if (n_sets < 0 || (n_sets > 0 && (!child || !set_offsets))) return fail(SSPS_ERR_INVALID, "ssps_score: bad argument");
+    if (logprior_out && !lambda) return fail(SSPS_ERR_INVALID, "ssps_score: logprior_out needs lambda");
+    if (n_sets == 0) return SSPS_OK;
+    const int V = h->V;
+    int kmax = 0;
+    for (int s = 0; s < n_sets; ++s) {
+        const int k = set_offsets[s + 1] - set_offsets[s];
+        if (k < 0 || k > V) return fail(SSPS_ERR_INVALID, "set %d has %d members", s, k);
+        if (child[s] < 0 || child[s] >= V) return fail(SSPS_ERR_INVALID, "set %d: child %d out of range", s, child[s]);
+        if (k > 0 && !set_members) return fail(SSPS_ERR_INVALID, "ssps_score: null set_members");
+        for (int a = 0; a < k; ++a) {
+            const int j = set_members[set_offsets[s] + a];
+            if (j < 0 || j >= V) return fail(SSPS_ERR_INVALID, "set %d: parent %d out of range", s, j);
+            if (a > 0 && j <= set_members[set_offsets[s] + a - 1])
+                return fail(SSPS_ERR_INVALID, "set %d: members must be sorted ascending and unique", s);
+        }
+        kmax = std::max(kmax, k);
+    }
+    const int total = set_offsets[n_sets];
+    const int kcap = std::max(kmax, 1);
+    const int block = 128, grid = div_up((size_t)n_sets, block);
+    const size_t nthreads = (size_t)grid * block;
+    DevBuf<int> d_child, d_off, d_mem;
+    DevBuf<double> d_lam, d_lml, d_lp, d_minp, arena_d;
+    DevBuf<uint16_t> arena_t;
+    CKS(upload(h, d_child, child, (size_t)n_sets));
+    CKS(upload(h, d_off, set_offsets, (size_t)n_sets + 1));
+    CKS(upload(h, d_mem, set_members, (size_t)total));
+    if (lambda) CKS(upload(h, d_lam, lambda, (size_t)n_sets));
+    CK(d_lml.alloc(n_sets)); CK(d_lp.alloc(n_sets)); CK(d_minp.alloc(n_sets));
+    CK(arena_d.alloc(nthreads * (size_t)(SSPS_TRI(kcap) + kcap)));
+    CK(arena_t.alloc(nthreads * (size_t)kcap));
+    score_kernel<<<grid, block, 0, h->stream>>>(h->dev, n_sets, d_child.p, d_off.p, d_mem.p, lambda ? d_lam.p : nullptr,
+                                                arena_d.p, arena_t.p, kcap, d_lml.p, logprior_out ? d_lp.p : nullptr, d_minp.p);
+    CKS(launch_ok(h, "score_kernel"));
+    if (lml_out) CKS(download(h, lml_out, d_lml.p, (size_t)n_sets));
+    if (logprior_out) CKS(download(h, logprior_out, d_lp.p, (size_t)n_sets));
+    if (min_pivot_out) CKS(download(h, min_pivot_out, d_minp.p, (size_t)n_sets));
+    CK(cudaStreamSynchronize(h->stream));
+    return SSPS_OK;
+}
+
+}  // extern "C"
+
+// ================================================================================================
+// chains: allocation, launches, snapshots, change-point log
+// ================================================================================================
+namespace {
+
+int alloc_chains(ssps_handle* h, int n_chains) {
+    const int V = h->V;
+    const size_t vv = (size_t)V * V;
+    h->n_chains = 0;
+    h->snaps.clear();
+    h->nch_pad = ((n_chains + 31) / 32) * 32;
+    int kcap = h->cfg.max_indegree > 0 ? h->cfg.max_indegree : std::min(V, 64);
+    h->kcap = std::min(kcap, V);
+    CK(h->k.alloc((size_t)V * h->nch_pad)); CK(h->lambda.alloc((size_t)V * h->nch_pad));
+    CK(h->slots.alloc(vv * h->nch_pad));
+    CK(h->counts.alloc(vv * n_chains));
+    CK(h->lam_sum.alloc((size_t)V * n_chains)); CK(h->lam_sq.alloc((size_t)V * n_chains));
+    cudaStream_t s = h->stream;
+    CK(cudaMemsetAsync(h->k.p, 0, h->k.bytes(), s));
+    CK(cudaMemsetAsync(h->lambda.p, 0, h->lambda.bytes(), s));
+    CK(cudaMemsetAsync(h->slots.p, 0, h->slots.bytes(), s));
+    CK(cudaMemsetAsync(h->counts.p, 0, h->counts.bytes(), s));
+    CK(cudaMemsetAsync(h->lam_sum.p, 0, h->lam_sum.bytes(), s));
+    CK(cudaMemsetAsync(h->lam_sq.p, 0, h->lam_sq.bytes(), s));
+    ChainState& st = h->st;
+    st.n_chains = n_chains; st.nch_pad = h->nch_pad;
+    st.k = h->k.p; st.lambda = h->lambda.p; st.slots = h->slots.p; st.counts = h->counts.p;
+    st.lam_sum = h->lam_sum.p; st.lam_sq = h->lam_sq.p;
+
+    // persistent MH grid: as many CTAs as stay resident, never more than there are warp-tasks
+    h->mh_smem = (size_t)(SSPS_TRI(SSPS_KS) + SSPS_KS) * sizeof(double) * SSPS_BLOCK + (size_t)SSPS_KS * sizeof(uint16_t) * SSPS_BLOCK;
+    int occ_p = 0, occ_r = 0;
+    CK(cudaFuncSetAttribute(mh_sweeps_kernel<PhiloxSource>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(mh_sweeps_kernel<ReplaySource>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_p, mh_sweeps_kernel<PhiloxSource>, SSPS_BLOCK, h->mh_smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_r, mh_sweeps_kernel<ReplaySource>, SSPS_BLOCK, h->mh_smem));
+    const int occ = std::max(1, std::min(occ_p, occ_r));
+    const int n_tasks = V * (h->nch_pad / 32);
+    const int warps_per_cta = SSPS_BLOCK / 32;
+    h->mh_grid = std::max(1, std::min(h->sm_count * occ, div_up((size_t)n_tasks, warps_per_cta)));
+    const size_t nthreads = (size_t)h->mh_grid * SSPS_BLOCK;
+    CK(h->arena_d.alloc(nthreads * (size_t)(SSPS_TRI(h->kcap) + h->kcap)));
+    CK(h->arena_t.alloc(nthreads * (size_t)h->kcap));
+    CK(h->task_counter.alloc(1));
+    CK(h->stats.alloc(8)); CK(h->khist.alloc(64));
+    CK(cudaMemsetAsync(h->stats.p, 0, h->stats.bytes(), s));
+    CK(cudaMemsetAsync(h->khist.p, 0, h->khist.bytes(), s));
+
+    h->thinning = 0; h->sweeps_done = 0; h->samples_recorded = 0;
+    h->kernel_ms = 0.0; h->mh_launches = 0;
+    h->snap_grid = h->cfg.psrf_grid == 0 ? 250 : (h->cfg.psrf_grid < 0 ? 0 : h->cfg.psrf_grid);
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    h->snap_budget_bytes = free_b / 4;
+
+    h->cp_parent.clear(); h->cp_lambda.clear(); h->cp_present.clear(); h->cp_lambda_last.clear();
+    h->pev_cap = h->lev_cap = 0;
+    h->n_chains = n_chains;
+    return SSPS_OK;
+}
+
+int fetch_state_host(ssps_handle* h, int chain, std::vector<int>& indeg, std::vector<int>& members_padded,
+                     std::vector<double>& lambda) {
+    const int V = h->V;
+    DevBuf<int> d_indeg, d_mem;
+    DevBuf<double> d_lam;
+    CK(d_indeg.alloc(V)); CK(d_mem.alloc((size_t)V * V)); CK(d_lam.alloc(V));
+    export_chain_kernel<<<div_up(V, 128), 128, 0, h->stream>>>(h->dev, h->st, chain, d_indeg.p, d_mem.p, d_lam.p);
+    CKS(launch_ok(h, "export_chain"));
+    indeg.resize(V); members_padded.resize((size_t)V * V); lambda.resize(V);
+    CKS(download(h, indeg.data(), d_indeg.p, (size_t)V));
+    CKS(download(h, members_padded.data(), d_mem.p, (size_t)V * V));
+    CKS(download(h, lambda.data(), d_lam.p, (size_t)V));
+    CK(cudaStreamSynchronize(h->stream));
+    return SSPS_OK;
+}
+
+// index 0 of the change-point log = the initial state (state_updates.jl:166-186)
+int changepoints_begin(ssps_handle* h) {
+    const int V = h->V, C = h->n_chains;
+    h->cp_parent.assign(C, {}); h->cp_lambda.assign(C, {});
+    h->cp_present.assign((size_t)C * V * V, 0);
+    h->cp_lambda_last.assign((size_t)C * V, 0.0);
+    std::vector<int> indeg, mem;
+    std::vector<double> lam;
+    for (int c = 0; c < C; ++c) {
+        CKS(fetch_state_host(h, c, indeg, mem, lam));
+        for (int i = 0; i < V; ++i) {
+            h->cp_lambda[c].push_back({0, i, lam[i]});
+            h->cp_lambda_last[(size_t)c * V + i] = lam[i];
+            for (int a = 0; a < indeg[i]; ++a) {
+                const int j = mem[(size_t)i * V + a];
+                h->cp_parent[c].push_back({0, i, j, 1});
+                h->cp_present[((size_t)c * V + i) * V + j] = 1;
+            }
+        }
+    }
+    return SSPS_OK;
+}
+
+int changepoints_alloc(ssps_handle* h, int max_rec_local, int max_sweeps_local) {
+    const size_t nmc = (size_t)h->n_chains * h->V;
+    const int pcap = 2 * max_sweeps_local, lcap = max_rec_local;
+    if (pcap > h->pev_cap) { CK(h->pev.alloc(nmc * pcap)); h->pev_cap = pcap; }
+    if (lcap > h->lev_cap) { CK(h->lev_val.alloc(nmc * lcap)); CK(h->lev_idx.alloc(nmc * lcap)); h->lev_cap = lcap; }
+    if (h->pev_n.n < nmc) { CK(h->pev_n.alloc(nmc)); CK(h->lev_n.alloc(nmc)); }
+    return SSPS_OK;
+}
+
+// Turn one launch's toggle log into change points relative to the previously RECORDED state.
+int changepoints_drain(ssps_handle* h, int64_t rec_base) {
+    const int V = h->V, C = h->n_chains;
+    const size_t nmc = (size_t)C * V;
+    std::vector<int> pn(nmc), ln(nmc);
+    std::vector<uint32_t> pev(nmc * h->pev_cap);
+    std::vector<double> lval(nmc * h->lev_cap);
+    std::vector<uint16_t> lidx(nmc * h->lev_cap);
+    CKS(download(h, pn.data(), h->pev_n.p, nmc));
+    CKS(download(h, ln.data(), h->lev_n.p, nmc));
+    CKS(download(h, pev.data(), h->pev.p, pev.size()));
+    CKS(download(h, lval.data(), h->lev_val.p, lval.size()));
+    CKS(download(h, lidx.data(), h->lev_idx.p, lidx.size()));
+    CK(cudaStreamSynchronize(h->stream));
+    std::vector<std::pair<int, int>> touched;   // (rel sample, parent)
+    for (int c = 0; c < C; ++c)
+        for (int i = 0; i < V; ++i) {
+            const size_t mc = (size_t)c * V + i;
+            if (pn[mc] > h->pev_cap || ln[mc] > h->lev_cap) return fail(SSPS_ERR_NOMEM, "change-point log overflow");
+            uint8_t* present = &h->cp_present[mc * V];
+            // toggles are in time order; those sharing a recorded-sample index collapse to their net effect
+            const uint32_t* ev = &pev[mc * h->pev_cap];
+            int a = 0;
+            while (a < pn[mc]) {
+                const int rel = (int)((ev[a] >> 16) & 0x7fffu);
+                int b = a;
+                touched.clear();
+                std::vector<uint8_t> now;   // small: at most 2 * thinning toggles
+                for (; b < pn[mc] && (int)((ev[b] >> 16) & 0x7fffu) == rel; ++b) {
+                    const int j = (int)(ev[b] & 0xffffu);
+                    const uint8_t val = (uint8_t)(ev[b] >> 31);
+                    bool found = false;
+                    for (size_t t = 0; t < touched.size(); ++t)
+                        if (touched[t].second == j) { now[t] = val; found = true; break; }
+                    if (!found) { touched.emplace_back(rel, j); now.push_back(val); }
+                }
+                std::vector<size_t> order(touched.size());
+                for (size_t t = 0; t < order.size(); ++t) order[t] = t;
+                std::sort(order.begin(), order.end(), [&](size_t x, size_t y) { return touched[x].second < touched[y].second; });
+                for (size_t t : order) {
+                    const int j = touched[t].second;
+                    if (present[j] != now[t]) {
+                        h->cp_parent[c].push_back({rec_base + rel, i, j, (int32_t)now[t]});
+                        present[j] = now[t];
+                    }
+                }
+                a = b;
+            }
+            for (int e = 0; e < ln[mc]; ++e) {
+                const double v = lval[mc * h->lev_cap + e];
+                h->cp_lambda[c].push_back({rec_base + (int64_t)lidx[mc * h->lev_cap + e], i, v});
+                h->cp_lambda_last[mc] = v;
+            }
+        }
+    return SSPS_OK;
+}
+
+int take_snapshot(ssps_handle* h) {
+    const size_t vv = (size_t)h->V * h->V;
+    const size_t per = vv * h->n_chains * sizeof(uint32_t) + 2 * (size_t)h->V * h->n_chains * sizeof(double);
+    // keep within budget: drop every other snapshot and double the grid
+    while (h->snap_grid > 0 && (h->snaps.size() + 1) * per > h->snap_budget_bytes && h->snaps.size() >= 2) {
+        h->snap_grid *= 2;
+        std::vector<Snapshot> kept;
+        for (auto& s : h->snaps)
+            if (s.n % h->snap_grid == 0) kept.push_back(std::move(s));
+        h->snaps.swap(kept);
+    }
+    if (h->snap_grid == 0 || h->samples_recorded % h->snap_grid != 0) return SSPS_OK;
+    Snapshot sn;
+    sn.n = h->samples_recorded;
+    CK(sn.counts.alloc(vv * h->n_chains)); CK(sn.lam_sum.alloc((size_t)h->V * h->n_chains)); CK(sn.lam_sq.alloc((size_t)h->V * h->n_chains));
+    CK(cudaMemcpyAsync(sn.counts.p, h->counts.p, sn.counts.bytes(), cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpyAsync(sn.lam_sum.p, h->lam_sum.p, sn.lam_sum.bytes(), cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpyAsync(sn.lam_sq.p, h->lam_sq.p, sn.lam_sq.bytes(), cudaMemcpyDeviceToDevice, h->stream));
+    h->snaps.push_back(std::move(sn));
+    return SSPS_OK;
+}
+
+const Snapshot* find_snapshot(const ssps_handle* h, int64_t n) {
+    for (const auto& s : h->snaps)
+        if (s.n == n) return &s;
+    return nullptr;
+}
+
+// One batch of sweeps for every micro-chain.  replay_dev == nullptr => Philox streams.
+int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning, const double* replay_host,
+               int64_t* sweeps_done_out) {
+    if (!h->has_data || h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "ssps_run before ssps_set_data / ssps_init_chains");
+    if (thinning < 1) return fail(SSPS_ERR_INVALID, "thinning must be >= 1");
+    if (n_sweeps < 0 || n_sweeps % thinning != 0) return fail(SSPS_ERR_INVALID, "n_sweeps must be a non-negative multiple of thinning");
+    if (h->thinning == 0) h->thinning = thinning;
+    if (h->thinning != thinning) return fail(SSPS_ERR_INVALID, "thinning changed from %d to %d between runs", h->thinning, thinning);
+    const int V = h->V, C = h->n_chains;
+    const bool log_cp = h->cfg.record_changepoints != 0;
+    const int64_t max_rec = log_cp ? 4096 : 30000;          // rel indices are 15/16-bit on the device
+    const int64_t dflt_rec = h->snap_grid > 0 ? h->snap_grid : 1024;
+    if (log_cp && h->cp_parent.empty()) CKS(changepoints_begin(h));
+
+    DevBuf<double> replay_dev;
+    if (replay_host) CKS(upload(h, replay_dev, replay_host, (size_t)n_sweeps * C * V * 6));
+
+    const auto t0 = std::chrono::steady_clock::now();
+    int64_t done = 0;
+    size_t ev_used = 0;
+    while (done < n_sweeps) {
+        if (timeout_s > 0.0) {
+            CK(cudaStreamSynchronize(h->stream));
+            const double el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            if (el >= timeout_s) break;
+        }
+        // launch boundary = next snapshot point (or the default batch), capped by the rel-index width
+        int64_t rec = std::min<int64_t>((n_sweeps - done) / thinning, std::min(max_rec, dflt_rec));
+        if (h->snap_grid > 0) rec = std::min(rec, h->snap_grid - h->samples_recorded % h->snap_grid);
+        const int n_local = (int)(rec * thinning);
+        MhParams prm{};
+        prm.sweep0 = h->sweeps_done; prm.n_local = n_local; prm.thinning = thinning;
+        prm.n_tasks = V * (h->nch_pad / 32);
+        prm.task_counter = h->task_counter.p;
+        prm.arena_d = h->arena_d.p; prm.arena_t = h->arena_t.p; prm.arena_kcap = h->kcap;
+        prm.arena_stride = h->mh_grid * SSPS_BLOCK;
+        prm.stats = h->stats.p;
+        prm.khist = h->cfg.collect_khist ? h->khist.p : nullptr;
+        if (log_cp) {
+            CKS(changepoints_alloc(h, (int)rec, n_local));
+            prm.pev = h->pev.p; prm.pev_n = h->pev_n.p; prm.pev_cap = h->pev_cap;
+            prm.lev_val = h->lev_val.p; prm.lev_idx = h->lev_idx.p; prm.lev_n = h->lev_n.p; prm.lev_cap = h->lev_cap;
+        }
+        CK(cudaMemsetAsync(h->task_counter.p, 0, sizeof(int), h->stream));
+        if (ev_used == h->ev_pool.size()) {
+            cudaEvent_t a, b;
+            CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+            h->ev_pool.emplace_back(a, b);
+        }
+        CK(cudaEventRecord(h->ev_pool[ev_used].first, h->stream));
+        if (replay_host) {
+            ReplaySource src{replay_dev.p + (size_t)done * C * V * 6, C, V};
+            mh_sweeps_kernel<ReplaySource><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+        } else {
+            PhiloxSource src{h->seed, h->chain_offset};
+            mh_sweeps_kernel<PhiloxSource><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+        }
+        CKS(launch_ok(h, "mh_sweeps_kernel"));
+        CK(cudaEventRecord(h->ev_pool[ev_used].second, h->stream));
+        ++ev_used; ++h->mh_launches;
+        const int64_t rec_base = h->samples_recorded;
+        h->sweeps_done += n_local; h->samples_recorded += rec; done += n_local;
+        if (log_cp) CKS(changepoints_drain(h, rec_base));
+        CKS(take_snapshot(h));
+        if (ev_used >= 256) {   // resolve timings in bounded batches
+            CK(cudaStreamSynchronize(h->stream));
+            for (size_t e = 0; e < ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
+            ev_used = 0;
+        }
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    for (size_t e = 0; e < ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
+    if (sweeps_done_out) *sweeps_done_out = done;
+    unsigned long long overflow = 0;
+    CK(cudaMemcpy(&overflow, h->stats.p + 5, sizeof overflow, cudaMemcpyDeviceToHost));
+    if (overflow) return fail(SSPS_ERR_INDEGREE, "a parent set exceeded max_indegree=%d; results are invalid, re-create with a larger bound", h->kcap);
+    return SSPS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ssps_init_chains(ssps_handle* h, int32_t n_chains, uint64_t seed, uint32_t chain_id_offset,
+                     const int32_t* init_offsets, const int32_t* init_members, const double* init_lambda) {
+    CKS(bind(h));
+    if (!h->has_data) return fail(SSPS_ERR_INVALID, "ssps_init_chains before ssps_set_data");
+    if (n_chains < 1) return fail(SSPS_ERR_INVALID, "n_chains must be >= 1");
+    const bool explicit_state = init_offsets || init_members || init_lambda;
+    if (explicit_state && (!init_offsets || !init_lambda))
+        return fail(SSPS_ERR_INVALID, "init_offsets / init_members / init_lambda are all-or-nothing");
+    CKS(alloc_chains(h, n_chains));
+    h->seed = seed; h->chain_offset = chain_id_offset;
+    const int V = h->V;
+    const size_t nmc = (size_t)n_chains * V;
+    const int blocks = div_up((size_t)V * h->nch_pad, 128);
+    if (explicit_state) {
+        for (size_t m = 0; m < nmc; ++m) {
+            const int k = init_offsets[m + 1] - init_offsets[m];
+            if (k < 0 || k > V) return fail(SSPS_ERR_INVALID, "initial parent set %zu has %d members", m, k);
+            if (k > 0 && !init_members) return fail(SSPS_ERR_INVALID, "null init_members");
+            for (int a = 0; a < k; ++a) {
+                const int j = init_members[init_offsets[m] + a];
+                if (j < 0 || j >= V || (a > 0 && j <= init_members[init_offsets[m] + a - 1]))
+                    return fail(SSPS_ERR_INVALID, "initial parent set %zu must be sorted, unique, in range", m);
+            }
+            const double l = init_lambda[m];
+            if (!(l >= h->lambda_min && l <= h->cfg.lambda_max))
+                return fail(SSPS_ERR_INVALID, "initial lambda %g outside [%g, %g]", l, h->lambda_min, h->cfg.lambda_max);
+        }
+        DevBuf<int> d_off, d_mem;
+        DevBuf<double> d_lam;
+        CKS(upload(h, d_off, init_offsets, nmc + 1));
+        CKS(upload(h, d_mem, init_members, (size_t)init_offsets[nmc]));
+        CKS(upload(h, d_lam, init_lambda, nmc));
+        import_state_kernel<<<blocks, 128, 0, h->stream>>>(h->dev, h->st, d_off.p, d_mem.p, d_lam.p);
+        CKS(launch_ok(h, "import_state"));
+        CK(cudaStreamSynchronize(h->stream));
+    } else {
+        init_chains_kernel<<<blocks, 128, 0, h->stream>>>(h->dev, h->st, seed, chain_id_offset);
+        CKS(launch_ok(h, "init_chains"));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return SSPS_OK;
+}
+
+int ssps_run(ssps_handle* h, int64_t n_sweeps, double timeout_s, int32_t thinning, int64_t* sweeps_done) {
+    CKS(bind(h));
+    return run_sweeps(h, n_sweeps, timeout_s, thinning, nullptr, sweeps_done);
+}
+
+int ssps_replay(ssps_handle* h, int64_t n_sweeps, const double* draws, int32_t thinning) {
+    CKS(bind(h));
+    if (!draws) return fail(SSPS_ERR_INVALID, "ssps_replay: null draws");
+    return run_sweeps(h, n_sweeps, 0.0, thinning, draws, nullptr);
+}
+
+int ssps_get_state(ssps_handle* h, int32_t chain, int32_t* indeg, int32_t* members, int64_t cap, int64_t* n_members,
+                   double* lambda, double* lml) {
+    CKS(bind(h));
+    if (h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "no chains");
+    if (chain < 0 || chain >= h->n_chains) return fail(SSPS_ERR_INVALID, "chain %d out of range", chain);
+    const int V = h->V;
+    std::vector<int> kk, mem;
+    std::vector<double> lam;
+    CKS(fetch_state_host(h, chain, kk, mem, lam));
+    int64_t total = 0;
+    for (int i = 0; i < V; ++i) total += kk[i];
+    if (n_members) *n_members = total;
+    if (indeg) memcpy(indeg, kk.data(), sizeof(int) * (size_t)V);
+    if (lambda) memcpy(lambda, lam.data(), sizeof(double) * (size_t)V);
+    if (members) {
+        if (cap < total) return fail(SSPS_ERR_INVALID, "members capacity %lld < %lld", (long long)cap, (long long)total);
+        int64_t o = 0;
+        for (int i = 0; i < V; ++i)
+            for (int a = 0; a < kk[i]; ++a) members[o++] = mem[(size_t)i * V + a];
+    }
+    if (lml) {
+        const int block = 128, grid = div_up((size_t)V, block);
+        const size_t nthreads = (size_t)grid * block;
+        DevBuf<double> d_lml, arena_d;
+        DevBuf<uint16_t> arena_t;
+        int kmax = 1;
+        for (int i = 0; i < V; ++i) kmax = std::max(kmax, kk[i]);
+        CK(d_lml.alloc(V)); CK(arena_d.alloc(nthreads * (size_t)(SSPS_TRI(kmax) + kmax))); CK(arena_t.alloc(nthreads * (size_t)kmax));
+        state_lml_kernel<<<grid, block, 0, h->stream>>>(h->dev, h->st, chain, arena_d.p, arena_t.p, kmax, (int)nthreads, d_lml.p);
+        CKS(launch_ok(h, "state_lml"));
+        CKS(download(h, lml, d_lml.p, (size_t)V));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return SSPS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// tallies / posterior / PSRF (K4)
+// ------------------------------------------------------------------------------------------------
+int ssps_edge_counts(ssps_handle* h, double* counts_child_major, int64_t* n_samples, int32_t* n_chains) {
+    CKS(bind(h));
+    if (h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "no chains");
+    const size_t vv = (size_t)h->V * h->V;
+    if (counts_child_major) {
+        DevBuf<double> out;
+        CK(out.alloc(vv));
+        edge_sum_kernel<<<div_up(vv, 256), 256, 0, h->stream>>>(h->counts.p, nullptr, h->n_chains, vv, out.p);
+        CKS(launch_ok(h, "edge_sum"));
+        CKS(download(h, counts_child_major, out.p, vv));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    if (n_samples) *n_samples = h->samples_recorded;
+    if (n_chains) *n_chains = h->n_chains;
+    return SSPS_OK;
+}
+
+int ssps_chain_edge_counts(ssps_handle* h, uint32_t* counts) {
+    CKS(bind(h));
+    if (h->n_chains <= 0 || !counts) return fail(SSPS_ERR_INVALID, "no chains / null buffer");
+    CKS(download(h, counts, h->counts.p, (size_t)h->V * h->V * h->n_chains));
+    CK(cudaStreamSynchronize(h->stream));
+    return SSPS_OK;
+}
+
+int ssps_edge_posterior(ssps_handle* h, double burnin, double* probs_child_major, double* lambda_mean,
+                        int64_t* burnin_used, int64_t* n_used) {
+    CKS(bind(h));
+    if (h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "no chains");
+    if (!(burnin >= 0.0 && burnin < 1.0)) return fail(SSPS_ERR_INVALID, "burnin must be in [0, 1)");
+    const int64_t n = h->samples_recorded;
+    if (n < 1) return fail(SSPS_ERR_UNAVAILABLE, "no recorded samples yet");
+    const int64_t want = (int64_t)floor(burnin * (double)n);   // postprocess_samples.jl:186
+    const Snapshot* lo = nullptr;
+    for (const auto& s : h->snaps)
+        if (s.n <= want && s.n < n) lo = &s;
+    const int64_t b = lo ? lo->n : 0;
+    const size_t vv = (size_t)h->V * h->V;
+    const double denom = (double)(n - b) * (double)h->n_chains;
+    if (probs_child_major) {
+        DevBuf<double> out;
+        CK(out.alloc(vv));
+        edge_sum_kernel<<<div_up(vv, 256), 256, 0, h->stream>>>(h->counts.p, lo ? lo->counts.p : nullptr, h->n_chains, vv, out.p);
+        CKS(launch_ok(h, "edge_sum"));
+        CKS(download(h, probs_child_major, out.p, vv));
+        CK(cudaStreamSynchronize(h->stream));
+        for (size_t e = 0; e < vv; ++e) probs_child_major[e] /= denom;
+    }
+    if (lambda_mean) {
+        DevBuf<double> out;
+        CK(out.alloc(h->V));
+        lam_sum_kernel<<<div_up((size_t)h->V, 128), 128, 0, h->stream>>>(h->lam_sum.p, lo ? lo->lam_sum.p : nullptr, h->n_chains, h->V, out.p);
+        CKS(launch_ok(h, "lam_sum"));
+        CKS(download(h, lambda_mean, out.p, (size_t)h->V));
+        CK(cudaStreamSynchronize(h->stream));
+        for (int i = 0; i < h->V; ++i) lambda_mean[i] /= denom;
+    }
+    if (burnin_used) *burnin_used = b;
+    if (n_used) *n_used = n;
+    return SSPS_OK;
+}
+
+int64_t ssps_psrf_sums_len(int32_t V) { return 3 * (int64_t)V * V + 3 * (int64_t)V + 2; }
+
+int ssps_psrf_sums(ssps_handle* h, double burnin, double* sums, int32_t on_device) {
+    CKS(bind(h));
+    if (h->n_chains <= 0 || !sums) return fail(SSPS_ERR_INVALID, "no chains / null buffer");
+    if (!(burnin >= 0.0 && burnin < 1.0)) return fail(SSPS_ERR_INVALID, "burnin must be in [0, 1)");
+    if (h->snap_grid <= 0) return fail(SSPS_ERR_UNAVAILABLE, "snapshots disabled (psrf_grid < 0)");
+    // largest usable length: len, burn-in index b and split index s must all have snapshots
+    // (evaluate_convergence, postprocess_samples.jl:167-168; b = 0 needs none)
+    const Snapshot *S_len = nullptr, *S_s = nullptr, *S_b = nullptr;
+    int64_t len = 0, b = 0, s = 0;
+    std::vector<int64_t> cand;
+    cand.push_back(h->samples_recorded);
+    for (auto it = h->snaps.rbegin(); it != h->snaps.rend(); ++it)
+        if (it->n < h->samples_recorded) cand.push_back(it->n);
+    bool ok = false;
+    for (int64_t L : cand) {
+        b = (int64_t)floor(burnin * (double)L);
+        s = b + (L - b) / 2;
+        if (s - b < 2 || L - s < 2) continue;
+        S_s = find_snapshot(h, s);
+        S_b = b == 0 ? nullptr : find_snapshot(h, b);
+        S_len = find_snapshot(h, L);
+        if (S_s && (b == 0 || S_b) && (S_len || L == h->samples_recorded)) { len = L; ok = true; break; }
+    }
+    if (!ok) return fail(SSPS_ERR_UNAVAILABLE, "no snapshot-aligned (burn-in, split, length) triple yet: %lld samples, grid %lld",
+                         (long long)h->samples_recorded, (long long)h->snap_grid);
+    const int V = h->V;
+    const size_t vv = (size_t)V * V;
+    const size_t total = (size_t)ssps_psrf_sums_len(V);
+    double* dst = sums;
+    if (!on_device) { CK(h->sums_scratch.alloc(total)); dst = h->sums_scratch.p; }
+    const double N1 = (double)(s - b), N2 = (double)(len - s);
+    const uint32_t* c_len = S_len ? S_len->counts.p : h->counts.p;
+    const double* ls_len = S_len ? S_len->lam_sum.p : h->lam_sum.p;
+    const double* lq_len = S_len ? S_len->lam_sq.p : h->lam_sq.p;
+    psrf_sums_kernel<<<div_up(vv, 256), 256, 0, h->stream>>>(c_len, S_s->counts.p, S_b ? S_b->counts.p : nullptr, h->n_chains, vv, N1, N2, dst);
+    CKS(launch_ok(h, "psrf_sums"));
+    psrf_lambda_sums_kernel<<<div_up((size_t)V, 128), 128, 0, h->stream>>>(ls_len, S_s->lam_sum.p, S_b ? S_b->lam_sum.p : nullptr, lq_len,
+                                                                        S_s->lam_sq.p, S_b ? S_b->lam_sq.p : nullptr, h->n_chains, V, N1, N2,
+                                                                        dst + 3 * vv);
+    CKS(launch_ok(h, "psrf_lambda_sums"));
+    // tail: number of half-chains H, and H * n (so that a SUM all-reduce over ranks keeps n = tail[1] / tail[0])
+    const double tail[2] = {2.0 * (double)h->n_chains, 2.0 * (double)h->n_chains * N1};
+    CK(cudaMemcpyAsync(dst + 3 * vv + 3 * (size_t)V, tail, sizeof tail, cudaMemcpyHostToDevice, h->stream));
+    if (!on_device) CKS(download(h, sums, dst, total));
+    CK(cudaStreamSynchronize(h->stream));
+    return SSPS_OK;
+}
+
+int ssps_psrf_finish(ssps_handle* h, const double* sums, int32_t on_device, double* max_edge_psrf,
+                     double* edge_psrf_child_major, double* lambda_psrf) {
+    CKS(bind(h));
+    if (!h->has_data || !sums) return fail(SSPS_ERR_INVALID, "no data / null buffer");
+    const int V = h->V;
+    const size_t vv = (size_t)V * V;
+    const size_t total = (size_t)ssps_psrf_sums_len(V);
+    const double* src = sums;
+    if (!on_device) {
+        CK(h->sums_scratch.alloc(total));
+        CK(cudaMemcpyAsync(h->sums_scratch.p, sums, total * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        src = h->sums_scratch.p;
+    }
+    double tail[2];
+    CK(cudaMemcpyAsync(tail, src + 3 * vv + 3 * (size_t)V, sizeof tail, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    const double H = tail[0], n = tail[1] / tail[0];
+    if (!(H >= 2.0) || !(n >= 2.0)) return fail(SSPS_ERR_INVALID, "psrf sums carry H=%g n=%g", H, n);
+    CK(h->psrf_scratch.alloc(vv + V));
+    CK(h->max_bits.alloc(1));
+    CK(cudaMemsetAsync(h->max_bits.p, 0, sizeof(unsigned long long), h->stream));
+    psrf_finish_kernel<<<div_up(vv, 256), 256, 0, h->stream>>>(src, vv, vv, H, n, h->psrf_scratch.p, h->max_bits.p);
+    CKS(launch_ok(h, "psrf_finish(edges)"));
+    psrf_finish_kernel<<<div_up((size_t)V, 128), 128, 0, h->stream>>>(src + 3 * vv, (size_t)V, (size_t)V, H, n, h->psrf_scratch.p + vv, nullptr);
+    CKS(launch_ok(h, "psrf_finish(lambda)"));
+    unsigned long long bits = 0;
+    CKS(download(h, &bits, h->max_bits.p, 1));
+    if (edge_psrf_child_major) CKS(download(h, edge_psrf_child_major, h->psrf_scratch.p, vv));
+    if (lambda_psrf) CKS(download(h, lambda_psrf, h->psrf_scratch.p + vv, (size_t)V));
+    CK(cudaStreamSynchronize(h->stream));
+    if (max_edge_psrf) {
+        double m;
+        memcpy(&m, &bits, sizeof m);
+        *max_edge_psrf = bits ? m : NAN;   // NaN: every edge indicator was constant (W == 0 everywhere)
+    }
+    return SSPS_OK;
+}
+
+int ssps_psrf(ssps_handle* h, double burnin, double* max_edge_psrf, double* edge_psrf_child_major) {
+    CKS(bind(h));
+    if (!h->has_data) return fail(SSPS_ERR_INVALID, "no data");
+    DevBuf<double> sums;
+    CK(sums.alloc((size_t)ssps_psrf_sums_len(h->V)));
+    CKS(ssps_psrf_sums(h, burnin, sums.p, 1));
+    return ssps_psrf_finish(h, sums.p, 1, max_edge_psrf, edge_psrf_child_major, nullptr);
+}
+
+// ------------------------------------------------------------------------------------------------
+// change-point log
+// ------------------------------------------------------------------------------------------------
+int ssps_changepoints_size(ssps_handle* h, int32_t chain, int64_t* n_parent_events, int64_t* n_lambda_events) {
+    CKS(bind(h));
+    if (!h->cfg.record_changepoints) return fail(SSPS_ERR_UNAVAILABLE, "record_changepoints was 0 at ssps_create");
+    if (chain < 0 || chain >= h->n_chains) return fail(SSPS_ERR_INVALID, "chain %d out of range", chain);
+    if (h->cp_parent.empty()) CKS(changepoints_begin(h));
+    if (n_parent_events) *n_parent_events = (int64_t)h->cp_parent[chain].size();
+    if (n_lambda_events) *n_lambda_events = (int64_t)h->cp_lambda[chain].size();
+    return SSPS_OK;
+}
+
+int ssps_changepoints_get(ssps_handle* h, int32_t chain, int64_t* pe_n, int32_t* pe_child, int32_t* pe_parent,
+                          int32_t* pe_value, int64_t* le_n, int32_t* le_child, double* le_value) {
+    int64_t np = 0, nl = 0;
+    CKS(ssps_changepoints_size(h, chain, &np, &nl));
+    std::vector<ParentEvent> pe = h->cp_parent[chain];
+    std::stable_sort(pe.begin(), pe.end(), [](const ParentEvent& a, const ParentEvent& b) {
+        if (a.child != b.child) return a.child < b.child;
+        if (a.parent != b.parent) return a.parent < b.parent;
+        return a.n < b.n;
+    });
+    for (int64_t e = 0; e < np; ++e) {
+        if (pe_n) pe_n[e] = pe[e].n;
+        if (pe_child) pe_child[e] = pe[e].child;
+        if (pe_parent) pe_parent[e] = pe[e].parent;
+        if (pe_value) pe_value[e] = pe[e].value;
+    }
+    std::vector<LambdaEvent> le = h->cp_lambda[chain];
+    std::stable_sort(le.begin(), le.end(), [](const LambdaEvent& a, const LambdaEvent& b) {
+        if (a.child != b.child) return a.child < b.child;
+        return a.n < b.n;
+    });
+    for (int64_t e = 0; e < nl; ++e) {
+        if (le_n) le_n[e] = le[e].n;
+        if (le_child) le_child[e] = le[e].child;
+        if (le_value) le_value[e] = le[e].value;
+    }
+    return SSPS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// stats / diagnostics
+// ------------------------------------------------------------------------------------------------
+int ssps_get_stats(ssps_handle* h, ssps_run_stats* out) {
+    CKS(bind(h));
+    if (!out) return fail(SSPS_ERR_INVALID, "null out");
+    memset(out, 0, sizeof *out);
+    out->kernel_launches = h->kernel_launches;
+    if (h->n_chains > 0) {
+        unsigned long long st[8];
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaMemcpy(st, h->stats.p, sizeof st, cudaMemcpyDeviceToHost));
+        out->sweeps_done = h->sweeps_done;
+        out->samples_recorded = h->samples_recorded;
+        out->n_proposals = (int64_t)st[6];
+        out->n_accepted = (int64_t)st[0];
+        out->n_lambda_accepted = (int64_t)st[1];
+        out->sum_k = (int64_t)st[2];
+        out->algorithmic_flops = (double)st[3] / 3.0;   // sum (k^3 + 6k^2 + 6k) / 3 = sum k^3/3 + 2k^2 + 2k
+        out->algorithmic_bytes = 8.0 * (double)st[4];
+        out->kernel_ms = h->kernel_ms;
+        out->mh_launches = h->mh_launches;
+    }
+    return SSPS_OK;
+}
+
+int ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len) {
+    CKS(bind(h));
+    if (!hist || len < 1) return fail(SSPS_ERR_INVALID, "bad buffer");
+    if (h->n_chains <= 0 || !h->cfg.collect_khist) return fail(SSPS_ERR_UNAVAILABLE, "collect_khist was 0 or no chains");
+    unsigned long long hh[64];
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(hh, h->khist.p, sizeof hh, cudaMemcpyDeviceToHost));
+    for (int a = 0; a < len; ++a) hist[a] = a < 64 ? (int64_t)hh[a] : 0;
+    return SSPS_OK;
+}
+
+int ssps_measure_fp64_peak(ssps_handle* h, double* tflops) {
+    CKS(bind(h));
+    if (!tflops) return fail(SSPS_ERR_INVALID, "null out");
+    const int block = 256, grid = h->sm_count * 8, iters = 1 << 16;
+    DevBuf<double> out;
+    CK(out.alloc((size_t)grid * block));
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {
+        CK(cudaEventRecord(a, h->stream));
+        dfma_peak_kernel<<<grid, block, 0, h->stream>>>(out.p, iters);
+        CK(cudaEventRecord(b, h->stream));
+        CKS(launch_ok(h, "dfma_peak"));
+        CK(cudaEventSynchronize(b));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, a, b));
+        const double flops = 2.0 * 8.0 * (double)iters * (double)grid * block;
+        if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    *tflops = best;
+    return SSPS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,40 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def c1():
+    """Config C1: the reference's shipped example (run_ssps/example_*), committed as a fixture."""
+    d = np.load(os.path.join(ROOT, "tests", "golden", "example_c1.npz"))
+    return {k: d[k] for k in d.files}
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from oracle import oracle as orc
+    orc.build()
+    return orc
+
+
+@pytest.fixture(scope="session")
+def c1_problem(c1, oracle):
+    return oracle.Problem(c1["Xminus"], c1["Xplus"], c1["prior"], large_indeg=20.0, lambda_max=15.0,
+                          lambda_prop_std=3.0)
+
+
+def make_synth(V, T=8, M=4, seed=20200701):
+    from ssps_b200.simulate import simulate
+    ds = simulate(V, T, M, seed=seed)
+    xm, xp = ds.lagged()
+    return ds, xm, xp

@@ -1,0 +1,318 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle.
+
+Levels (BASELINE.json north_star / SURVEY 8c):
+  L1  lml / logprior for fixed parent sets: <= 1e-10 relative vs the reference-faithful QR oracle;
+  L2  replayed random stream: accept/reject decisions and parent sets bit-exact vs the
+      kernel-faithful (Gram-Cholesky) oracle;
+  L3  edge posteriors within Monte-Carlo error (test_gpu_posterior.py).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from conftest import make_synth  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def smp_c1(c1):
+    from ssps_b200 import Sampler
+    s = Sampler(large_indeg=20.0, lambda_max=15.0, lambda_prop_std=3.0, record_changepoints=True, psrf_grid=50)
+    s.set_data(c1["Xminus"], c1["Xplus"], c1["prior"])
+    yield s
+    s.close()
+
+
+# ---------------------------------------------------------------------------------------- K1
+def test_k1_design_and_gram_bit_exact(smp_c1, c1_problem):
+    Z, Y = smp_c1.design()
+    G, R, yty = smp_c1.gram()
+    assert np.array_equal(Z, c1_problem.Z)
+    assert np.array_equal(Y, c1_problem.Y)
+    assert np.array_equal(G, c1_problem.G)
+    assert np.array_equal(R, c1_problem.R)
+    assert np.array_equal(yty, c1_problem.yty)
+    # quirk Q4: G_jj = y'y = n - 1 after ddof-1 standardisation
+    assert np.allclose(np.diag(G), c1_problem.n - 1, rtol=1e-13)
+
+
+def test_k1_timeseries_lagging_matches_set_data(c1, c1_problem):
+    from ssps_b200 import Sampler
+    lens = c1["series_lengths"]
+    # rebuild the sorted per-series matrices exactly like ingest_timeseries!
+    raw, ser, ts = c1["raw_table"], c1["raw_series"], c1["raw_timestep"]
+    series, seen = [], []
+    for name in ser:
+        if name not in seen:
+            seen.append(name)
+    for name in seen:
+        idx = np.flatnonzero(ser == name)
+        idx = idx[np.argsort(ts[idx], kind="stable")]
+        series.append(raw[idx])
+    assert [s.shape[0] for s in series] == list(lens)
+    with Sampler(large_indeg=20.0, lambda_prop_std=3.0) as s:
+        s.set_timeseries(series, c1["prior"])
+        G, R, yty = s.gram()
+        assert s.n == c1_problem.n
+    assert np.array_equal(G, c1_problem.G) and np.array_equal(R, c1_problem.R)
+
+
+def test_k1_derived_parameters(smp_c1, c1_problem):
+    lmin, pp = smp_c1.derived()
+    assert lmin == c1_problem.lambda_min == 0.5
+    np.testing.assert_allclose(pp, c1_problem.prob_param, rtol=1e-14)
+
+
+# ---------------------------------------------------------------------------------------- K2 / L1
+def _random_sets(rng, V, n_sets, kmax):
+    ch = rng.integers(0, V, n_sets)
+    sets = [sorted(rng.choice(V, size=int(rng.integers(0, kmax + 1)), replace=False).tolist()) for _ in range(n_sets)]
+    return ch, sets
+
+
+def test_l1_known_answers(smp_c1, c1_problem):
+    n = c1_problem.n
+    # k = 0 closed form: lml = -n/2 log(n-1)  (-25.498920096505945 on C1)
+    assert smp_c1.log_marg_lik(0, []) == pytest.approx(-0.5 * n * np.log(n - 1.0), rel=1e-14)
+    assert smp_c1.log_marg_lik(0, []) == pytest.approx(-25.498920096505945, rel=1e-13)
+    assert smp_c1.log_marg_lik(0, [0]) == pytest.approx(-25.18530501424099, rel=1e-12)
+    assert smp_c1.log_marg_lik(4, [0, 1, 2]) == pytest.approx(-21.840418654218517, rel=1e-12)
+    assert smp_c1.conf_parents_logpdf([], 0, 3.0) == pytest.approx(-3.4002225376375375, rel=1e-13)
+    assert smp_c1.conf_parents_logpdf([1], 0, 3.0) == pytest.approx(-5.800222537637539, rel=1e-13)
+
+
+def test_l1_lml_vs_qr_oracle_c1(smp_c1, c1_problem, oracle):
+    rng = np.random.default_rng(1)
+    V = c1_problem.V
+    ch, sets = _random_sets(rng, V, 600, 12)
+    lam = rng.uniform(0.5, 15.0, len(sets))
+    lml, lp, minp = smp_c1.score(ch, sets, lam, want_min_pivot=True)
+    checked = 0
+    for s in range(len(sets)):
+        ref = c1_problem.lml(int(ch[s]), sets[s], oracle.SCORER_QR)
+        chol = c1_problem.lml(int(ch[s]), sets[s], oracle.SCORER_CHOL)
+        assert lml[s] == pytest.approx(chol, rel=1e-13)            # same arithmetic order; only log() differs
+        if minp[s] > 1e-5:                                       # cond(G_SS) well below 1e8
+            assert lml[s] == pytest.approx(ref, rel=1e-10)
+            checked += 1
+        assert lp[s] == pytest.approx(c1_problem.logprior(int(ch[s]), sets[s], lam[s], 0), rel=1e-11)
+        assert lp[s] == pytest.approx(c1_problem.logprior(int(ch[s]), sets[s], lam[s], 2), rel=1e-13)
+    assert checked > 400
+
+
+def test_l1_saturated_sets(smp_c1, c1_problem, oracle):
+    # |S| >= n-1 (n = 18): the projection saturates, lml = -k/2 log(1+n) - n/2 log((n-1)/(n+1))  
+    rng = np.random.default_rng(2)
+    n, V = c1_problem.n, c1_problem.V
+    for k in (n - 1, n, n + 3, 30, V):
+        S = sorted(rng.choice(V, size=k, replace=False).tolist())
+        closed = -0.5 * k * np.log(1.0 + n) - 0.5 * n * np.log((n - 1.0) / (n + 1.0))
+        got = smp_c1.log_marg_lik(3, S)
+        assert got == pytest.approx(closed, rel=1e-8)
+        assert got == pytest.approx(c1_problem.lml(3, S, oracle.SCORER_CHOL), rel=1e-12)
+
+
+def test_l1_synthetic_v100(oracle):
+    from ssps_b200 import Sampler
+    ds, xm, xp = make_synth(100)
+    P = oracle.Problem(xm, xp, ds.prior_graph, large_indeg=15.0, lambda_prop_std=3.0)
+    rng = np.random.default_rng(3)
+    ch, sets = _random_sets(rng, 100, 400, 6)
+    lam = rng.uniform(P.lambda_min, 15.0, len(sets))
+    with Sampler(large_indeg=15.0, lambda_prop_std=3.0) as s:
+        s.set_data(xm, xp, ds.prior_graph)
+        assert np.array_equal(s.gram()[0], P.G)
+        lml, lp, minp = s.score(ch, sets, lam, want_min_pivot=True)
+    n_ok = 0
+    for e in range(len(sets)):
+        assert lml[e] == pytest.approx(P.lml(int(ch[e]), sets[e], oracle.SCORER_CHOL), rel=1e-12)
+        assert lp[e] == pytest.approx(P.logprior(int(ch[e]), sets[e], lam[e], 0), rel=1e-11)
+        if minp[e] > 1e-4:
+            assert lml[e] == pytest.approx(P.lml(int(ch[e]), sets[e], oracle.SCORER_QR), rel=1e-10)
+            n_ok += 1
+    assert n_ok > 50
+
+
+def test_score_rejects_bad_input(smp_c1):
+    from ssps_b200 import SspsError
+    with pytest.raises(SspsError):
+        smp_c1.score([0], [[3, 2]])          # unsorted
+    with pytest.raises(SspsError):
+        smp_c1.score([99], [[1]])            # child out of range
+    with pytest.raises(SspsError):
+        smp_c1.score([0], [[46]])            # parent out of range
+    lml, _ = smp_c1.score([], [])
+    assert lml.shape == (0,)
+
+
+# ---------------------------------------------------------------------------------------- K3 / L2
+def _oracle_chains(oracle, P, n_chains, seed, chain_offset=0):
+    chains = []
+    for c in range(n_chains):
+        ch = oracle.Chain(P, scorer=oracle.SCORER_CHOL)
+        ch.init(seed, chain_offset + c)
+        chains.append(ch)
+    return chains
+
+
+def test_init_matches_oracle(smp_c1, c1_problem, oracle):
+    smp_c1.generate(5, seed=11, chain_id_offset=3)
+    chains = _oracle_chains(oracle, c1_problem, 5, 11, 3)
+    for c in range(5):
+        sets, lam, lml = smp_c1.state(c)
+        assert sets == chains[c].parent_sets()
+        np.testing.assert_allclose(lam, chains[c].lambdas(), rtol=1e-15)
+        np.testing.assert_allclose(lml, chains[c].lmls(), rtol=1e-12)
+
+
+@pytest.mark.parametrize("thinning", [1, 3])
+def test_l2_replay_bit_exact_c1(smp_c1, c1_problem, oracle, thinning):
+    n_chains, n_sweeps, V = 6, 60, c1_problem.V
+    rng = np.random.default_rng(100 + thinning)
+    draws = rng.random((n_sweeps, n_chains, V, 6))
+    draws[..., 0] = rng.standard_normal((n_sweeps, n_chains, V))
+    smp_c1.generate(n_chains, seed=5)
+    chains = _oracle_chains(oracle, c1_problem, n_chains, 5)
+    for ch in chains:
+        ch.recorder_enable()
+    smp_c1.replay(draws, thinning=thinning)
+    for c, ch in enumerate(chains):
+        for s in range(n_sweeps):
+            ch.sweep(draws[s, c])
+            if (s + 1) % thinning == 0:
+                ch.record()
+        sets, lam, lml = smp_c1.state(c)
+        assert sets == ch.parent_sets()                      # bit-exact decisions => identical sets
+        assert np.array_equal(lam, ch.lambdas())             # lambda = lambda + sigma z: exact
+        np.testing.assert_allclose(lml, ch.lmls(), rtol=1e-12)
+    cnt = smp_c1.chain_edge_counts()
+    for c, ch in enumerate(chains):
+        assert np.array_equal(cnt[c].astype(np.int64), ch.edge_counts())
+        # change-point log == update_results_storediff
+        got = smp_c1.results(c)
+        want = ch.results_dict()
+        assert got["n"] == want["n"] == n_sweeps // thinning
+        assert got["parent_sets"] == want["parent_sets"]
+        assert got["lambda"] == want["lambda"]
+    st = smp_c1.stats()
+    assert st.n_proposals == n_chains * V * n_sweeps
+    assert st.n_accepted == sum(ch.n_accepted for ch in chains)
+
+
+def test_l2_philox_run_matches_oracle(smp_c1, c1_problem, oracle):
+    # same Philox convention on both sides; Box-Muller's log/cos may differ in the last ulp between
+    # CUDA and glibc, so lambda is compared to 1e-12 and parent sets exactly
+    n_chains, n_sweeps = 4, 40
+    smp_c1.generate(n_chains, seed=77, chain_id_offset=9)
+    chains = _oracle_chains(oracle, c1_problem, n_chains, 77, 9)
+    assert smp_c1.update_loop(n_sweeps) == n_sweeps
+    for c, ch in enumerate(chains):
+        ch.run(n_sweeps)
+        sets, lam, _ = smp_c1.state(c)
+        assert sets == ch.parent_sets()
+        np.testing.assert_allclose(lam, ch.lambdas(), rtol=1e-12)
+
+
+def test_l2_replay_synthetic_v40(oracle):
+    from ssps_b200 import Sampler
+    ds, xm, xp = make_synth(40, seed=20200702)
+    P = oracle.Problem(xm, xp, ds.prior_graph, large_indeg=15.0, lambda_prop_std=3.0)
+    n_chains, n_sweeps, V = 33, 50, 40        # 33: a ragged last warp
+    rng = np.random.default_rng(7)
+    draws = rng.random((n_sweeps, n_chains, V, 6))
+    draws[..., 0] = rng.standard_normal((n_sweeps, n_chains, V))
+    with Sampler(large_indeg=15.0, lambda_prop_std=3.0) as s:
+        s.set_data(xm, xp, ds.prior_graph)
+        s.generate(n_chains, seed=1)
+        s.replay(draws)
+        chains = _oracle_chains(oracle, P, n_chains, 1)
+        for c, ch in enumerate(chains):
+            for t in range(n_sweeps):
+                ch.sweep(draws[t, c])
+            sets, lam, _ = s.state(c)
+            assert sets == ch.parent_sets()
+            assert np.array_equal(lam, ch.lambdas())
+
+
+def test_resume_from_explicit_state(smp_c1, c1_problem, oracle):
+    V = c1_problem.V
+    rng = np.random.default_rng(9)
+    psets = [sorted(rng.choice(V, size=int(rng.integers(0, 6)), replace=False).tolist()) for _ in range(V)]
+    lam = rng.uniform(0.5, 15.0, V)
+    smp_c1.generate(2, seed=3, init_parent_sets=[psets, psets], init_lambda=[lam, lam])
+    sets, lam_got, lml = smp_c1.state(1)
+    assert sets == psets and np.array_equal(lam_got, lam)
+    ch = oracle.Chain(c1_problem, scorer=oracle.SCORER_CHOL)
+    ch.set_state(psets, lam)
+    np.testing.assert_allclose(lml, ch.lmls(), rtol=1e-12)
+    # index 0 of the change-point log is the initial state
+    res = smp_c1.results(0)
+    assert res["n"] == 0
+    for i in range(V):
+        assert sorted(int(k) - 1 for k in res["parent_sets"][i]) == psets[i]
+        assert res["lambda"][i] == [[0, lam[i]]]
+
+
+# ---------------------------------------------------------------------------------------- K4
+def test_psrf_and_posterior_vs_oracle(c1, c1_problem, oracle):
+    from ssps_b200 import Sampler
+    n_chains, n_sweeps, V = 4, 400, c1_problem.V
+    with Sampler(large_indeg=20.0, lambda_prop_std=3.0, psrf_grid=50) as s:
+        s.set_data(c1["Xminus"], c1["Xplus"], c1["prior"])
+        s.generate(n_chains, seed=21)
+        s.update_loop(n_sweeps)
+        mx, edge = s.psrf(0.5)
+        probs, lam_mean, b_used, n_used = s.edge_posterior(0.5)
+        cnt, ns, nc = s.edge_counts()
+    assert (b_used, n_used, ns, nc) == (200, 400, 400, n_chains)
+    # oracle chains with dense indicator sequences
+    chains = _oracle_chains(oracle, c1_problem, n_chains, 21)
+    seqs = np.zeros((n_chains, V, V, n_sweeps), dtype=np.uint8)
+    lam_seq = np.zeros((n_chains, V, n_sweeps))
+    for c, ch in enumerate(chains):
+        for t in range(n_sweeps):
+            ch.sweep()
+            for i, ps in enumerate(ch.parent_sets()):
+                seqs[c, i, ps, t] = 1
+            lam_seq[c, :, t] = ch.lambdas()
+    assert np.array_equal(cnt, seqs.sum(axis=(0, 3)))
+    want_probs = seqs[:, :, :, 200:].sum(axis=(0, 3)) / (n_chains * 200.0)     # evaluate_summary
+    np.testing.assert_allclose(probs, want_probs, rtol=1e-13, atol=1e-15)
+    np.testing.assert_allclose(lam_mean, lam_seq[:, :, 200:].mean(axis=(0, 2)), rtol=1e-9)
+    worst = 0.0
+    for i in range(V):
+        for j in range(V):
+            want = oracle.psrf_binary_dense([seqs[c, i, j] for c in range(n_chains)], 0.5)
+            if np.isfinite(want):
+                assert edge[i, j] == pytest.approx(want, rel=1e-9)
+                worst = max(worst, want)
+            else:
+                assert not np.isfinite(edge[i, j])
+    assert mx == pytest.approx(worst, rel=1e-9)
+
+
+def test_full_size_properties_metric_point():
+    """Size-independent properties at the bench workload (V=100, n=28): tallies are consistent
+    with the sample count, the swap move preserves in-degree bookkeeping, stats add up."""
+    from ssps_b200 import Sampler
+    ds, xm, xp = make_synth(100)
+    n_chains, n_sweeps = 256, 300
+    with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=100, collect_khist=True) as s:
+        s.set_data(xm, xp, ds.prior_graph)
+        s.generate(n_chains, seed=5)
+        s.update_loop(n_sweeps)
+        st = s.stats()
+        cnt = s.chain_edge_counts()
+        hist = s.khist()
+        sets, lam, lml = s.state(17)
+        lmin, _ = s.derived()
+        probs, _, b_used, n_used = s.edge_posterior(0.5)
+        relml, _ = s.score(list(range(100)), sets)
+    assert st.n_proposals == n_chains * 100 * n_sweeps == hist.sum()
+    assert 0 < st.n_accepted < st.n_proposals
+    assert cnt.max() <= n_sweeps
+    assert (lam >= lmin).all() and (lam <= 15.0).all()
+    assert all(s_ == sorted(set(s_)) for s_ in sets)
+    np.testing.assert_allclose(lml, relml, rtol=1e-13)      # cached lml of the state == fresh score
+    assert (b_used, n_used) == (100, 300)
+    assert ((probs >= 0) & (probs <= 1)).all()
