@@ -148,7 +148,7 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    smp = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=S)
+    smp = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=max(S // 4, 1))
     smp.set_stream(stream.cuda_stream)
     smp.set_data(xm, xp, ds.prior_graph)
     smp.generate(C, seed=args.seed, chain_id_offset=rank * C)
@@ -167,7 +167,10 @@ def run_ours(args, rank, world, local_rank):
 
     for _ in range(args.warmup):
         step()
-    psrf_exchange()
+    try:
+        psrf_exchange()          # warm the PSRF kernels / NCCL; may be unavailable this early
+    except Exception:
+        pass
     st0 = smp.stats()
     barrier()
     clk = ClockSampler(local_rank)
@@ -271,7 +274,7 @@ def main():
     ap.add_argument("--T", type=int, default=8)
     ap.add_argument("--M", type=int, default=4)
     ap.add_argument("--chains", type=int, default=4096, help="chains per GPU")
-    ap.add_argument("--sweeps", type=int, default=200, help="sweeps per step")
+    ap.add_argument("--sweeps", type=int, default=400, help="sweeps per step")
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--large-indeg", type=float, default=15.0)
     ap.add_argument("--lambda-prop-std", type=float, default=3.0)

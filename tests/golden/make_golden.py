@@ -20,8 +20,8 @@ OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "example_c1.npz")
 
 
 def main():
-    ts = pd.read_csv(os.path.join(REF, "run_ssps/example_timeseries.csv"), sep="\t")
-    prior = pd.read_csv(os.path.join(REF, "run_ssps/example_prior.csv"), header=None).to_numpy(dtype=np.float64)
+    ts = pd.read_csv(os.path.join(REF, "run_ssps/example_timeseries.csv"), sep="\t", float_precision="round_trip")
+    prior = pd.read_csv(os.path.join(REF, "run_ssps/example_prior.csv"), header=None, float_precision="round_trip").to_numpy(dtype=np.float64)
     names = json.load(open(os.path.join(REF, "run_ssps/example_node_names.json")))
     var_names = list(ts.columns[2:])
     series_names, series = [], []
