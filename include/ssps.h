@@ -24,6 +24,9 @@
  *        smart_proposal / smart_involution              SSPS/src/dbn_proposals.jl:60-130
  *        lambda_vec_proposal                            SSPS/src/dbn_proposals.jl:244-248
  *        Gen.mh acceptance (Gen 0.4.5, not in tree)     call sites state_updates.jl:44-47
+ *   ssps_export_draws
+ *        the stream of Gen.normal / rand() / categorical / uniform_discrete draws of the sweep
+ *        (Gen 0.4.5 samplers; call sites SSPS/src/dbn_proposals.jl:67-77,246)
  *   ssps_edge_counts / ssps_edge_posterior
  *        increment_counts! / update_results_summary     SSPS/src/state_updates.jl:120-140,240-249
  *        evaluate_summary                               scripts/postprocess_samples.jl:183-191
@@ -48,7 +51,7 @@
 extern "C" {
 #endif
 
-#define SSPS_ABI_VERSION 1
+#define SSPS_ABI_VERSION 2
 
 typedef enum {
     SSPS_OK = 0,
@@ -75,7 +78,8 @@ typedef struct {
                                  (0 = default 250, <0 = never) */
     int32_t record_changepoints; /* 1: keep the reference's change-point log (small runs only) */
     int32_t collect_khist;    /* 1: histogram of proposed |S'| (diagnostics; slower) */
-    int32_t reserved;
+    int32_t verify;           /* 1: additionally score EVERY proposal from scratch (O(k^3)) and count proposals whose
+                                 incrementally maintained factor gives a different score (diagnostics; much slower) */
 } ssps_config;
 
 typedef struct {
@@ -90,6 +94,12 @@ typedef struct {
     double  kernel_ms;          /* device time of the MH kernel launches (CUDA events) */
     int64_t kernel_launches;    /* all kernels launched by this handle */
     int64_t mh_launches;        /* MH sweep kernel launches */
+    /* diagnostics of the MH kernel (csrc/ssps_mh.cuh): */
+    int64_t n_tier1;            /* parent-set tests whose fp32 screening was too close: redone in reference order, fp64 logs */
+    int64_t n_lambda_exact;     /* lambda-move tests redone in reference order */
+    int64_t n_big_steps;        /* proposals of lanes whose factor lives in the global-memory tier (|S| > 6) */
+    int64_t n_mismatch;         /* verify = 1 only: proposals whose cached-factor score differs from the from-scratch
+                                   score of the same parent list by even one bit (must be 0) */
 } ssps_run_stats;
 
 const char* ssps_last_error(void);
@@ -137,6 +147,11 @@ int  ssps_run(ssps_handle* h, int64_t n_sweeps, double timeout_s, int32_t thinni
 /* Same sweeps, but driven by a recorded stream: draws is n_sweeps x n_chains x V x 6 doubles
  * (z_lambda, u_lambda, u_action, u_add, u_rem, u_accept), host memory. */
 int  ssps_replay(ssps_handle* h, int64_t n_sweeps, const double* draws, int32_t thinning);
+
+/* The random numbers ssps_run will use (or used) for sweeps first_sweep+1 .. first_sweep+n_sweeps of the
+ * local chains, in ssps_replay's layout: out[n_sweeps][n_chains][V][6], host memory.  Feeding them to
+ * ssps_replay (or to the CPU oracle) from the same initial state reproduces ssps_run bit for bit. */
+int  ssps_export_draws(ssps_handle* h, int64_t first_sweep, int64_t n_sweeps, double* out);
 
 /* Current state of one chain: indeg[V], members (concatenated sorted parent lists, capacity cap,
  * *n_members = total), lambda[V], lml[V] (any may be NULL). */

@@ -213,7 +213,8 @@ double orc_lml_qr(const double* Xminus, const double* y, int n, const int* S, in
 
 /* ------------------------------------------------------------------------------------------
  * Kernel-faithful scorer (deg 1 only): B = Z[:,S]  =>  q = r_S' G_SS^-1 r_S, computed by a
- * row-by-row Cholesky over the SORTED S with column skipping: a column whose Schur pivot
+ * row-by-row Cholesky over S IN THE ORDER GIVEN (the chain passes the arrival order, ssps_score
+ * callers the sorted list) with column skipping: a column whose Schur pivot
  * d^2 <= 2^-40 * G_jj is numerically dependent on the earlier ones and contributes nothing
  * (its row of L and its w are zeroed), so q stays the squared norm of the projection -- the
  * rank-deficient semantics of the reference's pivoted QR ("hard parts").
@@ -612,7 +613,10 @@ struct orc_chain {
     int scorer, flags;
     uint64_t seed; uint32_t chain_id;
     int64_t sweeps;
-    int* k; int* S;          /* S: V rows of capacity V */
+    int* k; int* S;          /* S: V rows of capacity V, sorted ascending */
+    int* A;                  /* the same sets in ARRIVAL order (initial state arrives sorted; an accepted add
+                                appends, a remove deletes in place, a swap deletes then appends): the order the
+                                kernel-faithful Cholesky scorer factorises in (csrc/ssps_mh.cuh) */
     double* lambda; double* lml; double* nrm; double* somc;
     double* lp;              /* ref-faithful: cached full logprior of the current state */
     int64_t n_prop, n_acc, cache_hits;
@@ -624,7 +628,11 @@ struct orc_chain {
     pev_list* pev; lev_list* lev; int* prevS; int* prevk; int64_t* counts;
 };
 
-static double chain_lml(orc_chain* C, int child, const int* S, int k) {
+/* S: sorted list (the reference's key / design-column order); A: the same set in arrival order.
+ * The Cholesky scorer factorises in arrival order (what the device caches incrementally); the
+ * reference-faithful QR scorer builds B(S) from the sorted list like construct_B does. */
+static double chain_lml(orc_chain* C, int child, const int* S, const int* A, int k) {
+    if (C->scorer == ORC_SCORER_CHOL) return orc_problem_lml(C->P, child, A, k, ORC_SCORER_CHOL);
     if (C->flags & ORC_FLAG_LML_CACHE) {
         uint64_t key = key_of(child, S, k);
         double v;
@@ -656,12 +664,13 @@ orc_chain* orc_chain_create(const orc_problem* P, int scorer, int flags) {
     C->P = P; C->scorer = scorer; C->flags = flags;
     C->k = (int*)calloc((size_t)V, sizeof(int));
     C->S = (int*)calloc((size_t)V * V, sizeof(int));
+    C->A = (int*)calloc((size_t)V * V, sizeof(int));
     C->lambda = (double*)calloc((size_t)V, sizeof(double));
     C->lml = (double*)calloc((size_t)V, sizeof(double));
     C->nrm = (double*)calloc((size_t)V, sizeof(double));
     C->somc = (double*)calloc((size_t)V, sizeof(double));
     C->lp = (double*)calloc((size_t)V, sizeof(double));
-    C->tmp = (int*)calloc((size_t)V + 1, sizeof(int));
+    C->tmp = (int*)calloc(2 * (size_t)V + 2, sizeof(int));
     C->khist_len = V + 1;
     C->khist = (int64_t*)calloc((size_t)V + 1, sizeof(int64_t));
     if (flags & ORC_FLAG_LML_CACHE) fpmap_init(&C->lml_cache, (size_t)1 << 18);
@@ -672,7 +681,7 @@ orc_chain* orc_chain_create(const orc_problem* P, int scorer, int flags) {
 void orc_chain_destroy(orc_chain* C) {
     if (!C) return;
     int V = C->P->V;
-    free(C->k); free(C->S); free(C->lambda); free(C->lml); free(C->nrm); free(C->somc); free(C->lp);
+    free(C->k); free(C->S); free(C->A); free(C->lambda); free(C->lml); free(C->nrm); free(C->somc); free(C->lp);
     free(C->tmp); free(C->khist);
     if (C->lml_cache.keys) fpmap_free(&C->lml_cache);
     if (C->prior_cache.keys) fpmap_free(&C->prior_cache);
@@ -689,7 +698,7 @@ void orc_chain_destroy(orc_chain* C) {
 static void chain_refresh_vertex(orc_chain* C, int i) {
     const orc_problem* P = C->P;
     int* S = C->S + (size_t)i * P->V;
-    C->lml[i] = chain_lml(C, i, S, C->k[i]);
+    C->lml[i] = chain_lml(C, i, S, C->A + (size_t)i * P->V, C->k[i]);
     C->nrm[i] = normaliser(P, i, C->lambda[i]);
     C->somc[i] = sum_omc(P, i, S, C->k[i]);
     C->lp[i] = chain_logprior_full(C, i, S, C->k[i], C->lambda[i]);
@@ -717,6 +726,7 @@ void orc_chain_init(orc_chain* C, uint64_t seed, uint32_t chain_id) {
             if (u32_to_unit(w[j & 3]) < p) S[k++] = j;
         }
         C->k[i] = k;
+        memcpy(C->A + (size_t)i * V, S, sizeof(int) * (size_t)k);
         chain_refresh_vertex(C, i);
     }
 }
@@ -727,6 +737,7 @@ void orc_chain_set_state(orc_chain* C, const int* offsets, const int* members, c
         int k = offsets[i + 1] - offsets[i];
         C->k[i] = k;
         memcpy(C->S + (size_t)i * V, members + offsets[i], sizeof(int) * (size_t)k);
+        memcpy(C->A + (size_t)i * V, members + offsets[i], sizeof(int) * (size_t)k);
         C->lambda[i] = lambda[i];
         chain_refresh_vertex(C, i);
     }
@@ -768,6 +779,8 @@ static void chain_step(orc_chain* C, int i, const double d[6], int* acc_out) {
     double cp1 = mvP[0], cp2 = mvP[0] + mvP[1];
     int action = u_act < cp1 ? ORC_ACT_ADD : (u_act < cp2 ? ORC_ACT_SWAP : ORC_ACT_REM);
     int* T = C->tmp;
+    int* TA = C->tmp + V + 1;      /* proposed set in arrival order */
+    int* Acur = C->A + (size_t)i * V;
     int kn = k, j_add = -1, j_rem = -1;
     double fwd = 0.0, bwd = 0.0;
     if (action == ORC_ACT_ADD || action == ORC_ACT_SWAP) {
@@ -792,6 +805,9 @@ static void chain_step(orc_chain* C, int i, const double d[6], int* acc_out) {
         }
         if (!placed) T[t++] = j_add;
         kn = t;
+        t = 0;
+        for (int a = 0; a < k; ++a) if (Acur[a] != j_rem) TA[t++] = Acur[a];
+        if (j_add >= 0) TA[t++] = j_add;
     }
     if (action == ORC_ACT_ADD) {
         fwd = mvL[0] - P->logint[V - k];
@@ -802,7 +818,7 @@ static void chain_step(orc_chain* C, int i, const double d[6], int* acc_out) {
     }
     ++C->n_prop;
     if (kn < C->khist_len) ++C->khist[kn];
-    double lml_new = chain_lml(C, i, T, kn);
+    double lml_new = chain_lml(C, i, T, TA, kn);
     double alpha, lp_new = 0.0;
     if (ref_mode || (C->flags & ORC_FLAG_STALE_PRIOR)) {
         lp_new = chain_logprior_full(C, i, T, kn, lam);
@@ -819,6 +835,7 @@ static void chain_step(orc_chain* C, int i, const double d[6], int* acc_out) {
     if (log(u_acc) < alpha) {
         acc_p = 1; ++C->n_acc;
         memcpy(S, T, sizeof(int) * (size_t)kn);
+        memcpy(Acur, TA, sizeof(int) * (size_t)kn);
         C->k[i] = kn;
         C->lml[i] = lml_new;
         C->somc[i] = sum_omc(P, i, S, kn);

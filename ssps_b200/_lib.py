@@ -26,7 +26,7 @@ class Config(C.Structure):
         ("struct_size", C.c_int32), ("device", C.c_int32), ("regression_deg", C.c_int32),
         ("max_indegree", C.c_int32), ("large_indeg", C.c_double), ("lambda_max", C.c_double),
         ("lambda_prop_std", C.c_double), ("psrf_grid", C.c_int32), ("record_changepoints", C.c_int32),
-        ("collect_khist", C.c_int32), ("reserved", C.c_int32),
+        ("collect_khist", C.c_int32), ("verify", C.c_int32),
     ]
 
 
@@ -37,6 +37,7 @@ class RunStats(C.Structure):
         ("n_accepted", C.c_int64), ("n_lambda_accepted", C.c_int64), ("sum_k", C.c_int64),
         ("algorithmic_flops", C.c_double), ("algorithmic_bytes", C.c_double), ("kernel_ms", C.c_double),
         ("kernel_launches", C.c_int64), ("mh_launches", C.c_int64),
+        ("n_tier1", C.c_int64), ("n_lambda_exact", C.c_int64), ("n_big_steps", C.c_int64), ("n_mismatch", C.c_int64),
     ]
 
 
@@ -57,6 +58,7 @@ SIGNATURES = {
     "ssps_init_chains": (C.c_int, [_hp, C.c_int32, C.c_uint64, C.c_uint32, _ip, _ip, _dp]),
     "ssps_run": (C.c_int, [_hp, C.c_int64, C.c_double, C.c_int32, _lp]),
     "ssps_replay": (C.c_int, [_hp, C.c_int64, _dp, C.c_int32]),
+    "ssps_export_draws": (C.c_int, [_hp, C.c_int64, C.c_int64, _dp]),
     "ssps_get_state": (C.c_int, [_hp, C.c_int32, _ip, _ip, C.c_int64, _lp, _dp, _dp]),
     "ssps_edge_counts": (C.c_int, [_hp, _dp, _lp, _ip]),
     "ssps_chain_edge_counts": (C.c_int, [_hp, _up]),
@@ -100,8 +102,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
         f = getattr(L, name)          # AttributeError if the symbol is missing: fail loudly
         f.restype = res
         f.argtypes = args
-    if L.ssps_abi_version() != 1:
-        raise ImportError("libssps_b200.so ABI version %d, binding expects 1" % L.ssps_abi_version())
+    if L.ssps_abi_version() != 2:
+        raise ImportError("libssps_b200.so ABI version %d, binding expects 2" % L.ssps_abi_version())
     _lib = L
     return L
 

@@ -12,6 +12,7 @@
 // (update_results_storediff, SSPS/src/state_updates.jl:161-227).
 #include "../../include/ssps.h"
 #include "ssps_kernels.cuh"
+#include "ssps_mh.cuh"
 
 #include <algorithm>
 #include <chrono>
@@ -19,6 +20,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <new>
 #include <string>
 #include <unordered_map>
@@ -97,7 +99,9 @@ struct ssps_handle {
     int n = 0, V = 0;
     bool has_data = false;
     DevBuf<double> Xminus, Xplus, Z, Y, G, R, yty, conf, omc, prob_param, mvP, mvLogP, logint, grp_omc, grp_mult;
-    DevBuf<int> grp_off;
+    DevBuf<int> grp_off, fgrp_off;
+    DevBuf<float2> fgrp;
+    DevBuf<float> lam_margin;
     double lambda_min = 0.0;
     SspsDev dev{};
 
@@ -114,10 +118,12 @@ struct ssps_handle {
     ChainState st{};
     int mh_grid = 0;
     size_t mh_smem = 0;
-    DevBuf<double> arena_d;
-    DevBuf<uint16_t> arena_t;
-    DevBuf<int> task_counter;
-    DevBuf<unsigned long long> stats, khist;
+    DevBuf<double> big_d, x_d;      // arenas: cached-inverse tier, exact scratch (per resident thread)
+    DevBuf<uint32_t> big_w;
+    DevBuf<uint16_t> big_r, x_t;
+    DevBuf<int> task_counter, order;
+    DevBuf<unsigned long long> stats, khist, vcost;
+    bool have_cost = false;         // vcost holds the previous launch's per-vertex cycles
 
     // ---- snapshots for split-PSRF / burn-in (K4) ----
     int64_t snap_grid = 0;          // in recorded samples; 0 = disabled
@@ -228,6 +234,24 @@ int finish_data(ssps_handle* h, const double* prior_host) {
         }
     }
     goff[V] = (int)gomc.size();
+    // fp32 screening tables of the lambda move: groups with 1-c != 0 (the others cancel in a difference)
+    std::vector<int> foff(V + 1, 0);
+    std::vector<float2> fg;
+    std::vector<float> fmarg(V, 0.f);
+    for (int i = 0; i < V; ++i) {
+        foff[i] = (int)fg.size();
+        double msum = 0.0;
+        for (int g = goff[i]; g < goff[i + 1]; ++g) {
+            if (gomc[g] == 0.0) continue;
+            fg.push_back(make_float2((float)(-gomc[g] * 1.4426950408889634), (float)(gmult[g] * 0.6931471805599453)));
+            msum += gmult[g];
+        }
+        fmarg[i] = (float)(1e-5 + 4e-6 * msum);
+    }
+    foff[V] = (int)fg.size();
+    CKS(upload(h, h->fgrp_off, foff.data(), foff.size()));
+    CKS(upload(h, h->fgrp, fg.data(), fg.size()));
+    CKS(upload(h, h->lam_margin, fmarg.data(), fmarg.size()));
     CKS(upload(h, h->grp_off, goff.data(), goff.size()));
     CKS(upload(h, h->grp_omc, gomc.data(), gomc.size()));
     CKS(upload(h, h->grp_mult, gmult.data(), gmult.size()));
@@ -241,6 +265,7 @@ int finish_data(ssps_handle* h, const double* prior_host) {
     d.G = h->G.p; d.R = h->R.p; d.yty = h->yty.p; d.omc = h->omc.p; d.conf = h->conf.p;
     d.grp_off = h->grp_off.p; d.grp_omc = h->grp_omc.p; d.grp_mult = h->grp_mult.p;
     d.mvP = h->mvP.p; d.mvLogP = h->mvLogP.p; d.logint = h->logint.p;
+    d.fgrp_off = h->fgrp_off.p; d.fgrp = h->fgrp.p; d.lam_margin = h->lam_margin.p;
     h->has_data = true;
     // any chains belong to the previous data set
     h->n_chains = 0;
@@ -462,23 +487,38 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     st.lam_sum = h->lam_sum.p; st.lam_sq = h->lam_sq.p;
 
     // persistent MH grid: as many CTAs as stay resident, never more than there are warp-tasks
-    h->mh_smem = (size_t)(SSPS_TRI(SSPS_KS) + SSPS_KS) * sizeof(double) * SSPS_BLOCK + (size_t)SSPS_KS * sizeof(uint16_t) * SSPS_BLOCK;
-    int occ_p = 0, occ_r = 0;
-    CK(cudaFuncSetAttribute(mh_sweeps_kernel<PhiloxSource>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CK(cudaFuncSetAttribute(mh_sweeps_kernel<ReplaySource>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_p, mh_sweeps_kernel<PhiloxSource>, SSPS_BLOCK, h->mh_smem));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_r, mh_sweeps_kernel<ReplaySource>, SSPS_BLOCK, h->mh_smem));
-    const int occ = std::max(1, std::min(occ_p, occ_r));
+    h->mh_smem = (size_t)2 * SSPS_ROWLEN(SSPS_KS) * sizeof(double) * SSPS_BLOCK + (size_t)SSPS_KS * sizeof(uint32_t) * SSPS_BLOCK
+               + (size_t)SSPS_KS * SSPS_BLOCK;
+    int occ = 1 << 30;
+    {
+        const void* fns[4] = {(const void*)mh_sweeps_kernel<PhiloxSource, false>, (const void*)mh_sweeps_kernel<PhiloxSource, true>,
+                              (const void*)mh_sweeps_kernel<ReplaySource, false>, (const void*)mh_sweeps_kernel<ReplaySource, true>};
+        for (const void* f : fns) {
+            int o = 0;
+            CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            CK(cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->mh_smem));
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, f, SSPS_BLOCK, h->mh_smem));
+            occ = std::min(occ, o);
+        }
+    }
+    occ = std::max(1, occ);
     const int n_tasks = V * (h->nch_pad / 32);
     const int warps_per_cta = SSPS_BLOCK / 32;
     h->mh_grid = std::max(1, std::min(h->sm_count * occ, div_up((size_t)n_tasks, warps_per_cta)));
     const size_t nthreads = (size_t)h->mh_grid * SSPS_BLOCK;
-    CK(h->arena_d.alloc(nthreads * (size_t)(SSPS_TRI(h->kcap) + h->kcap)));
-    CK(h->arena_t.alloc(nthreads * (size_t)h->kcap));
+    const size_t kc = (size_t)h->kcap;
+    CK(h->big_d.alloc(nthreads * 2 * SSPS_ROWLEN(kc)));
+    CK(h->big_w.alloc(nthreads * kc));
+    CK(h->big_r.alloc(nthreads * kc));
+    CK(h->x_d.alloc(nthreads * (SSPS_TRI(kc) + kc)));
+    CK(h->x_t.alloc(nthreads * 2 * kc));
     CK(h->task_counter.alloc(1));
-    CK(h->stats.alloc(8)); CK(h->khist.alloc(64));
+    CK(h->order.alloc(V)); CK(h->vcost.alloc(V));
+    CK(h->stats.alloc(ST_N)); CK(h->khist.alloc(64));
     CK(cudaMemsetAsync(h->stats.p, 0, h->stats.bytes(), s));
     CK(cudaMemsetAsync(h->khist.p, 0, h->khist.bytes(), s));
+    CK(cudaMemsetAsync(h->vcost.p, 0, h->vcost.bytes(), s));
+    h->have_cost = false;
 
     h->thinning = 0; h->sweeps_done = 0; h->samples_recorded = 0;
     h->kernel_ms = 0.0; h->mh_launches = 0;
@@ -658,10 +698,13 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
         const int n_local = (int)(rec * thinning);
         MhParams prm{};
         prm.sweep0 = h->sweeps_done; prm.n_local = n_local; prm.thinning = thinning;
-        prm.n_tasks = V * (h->nch_pad / 32);
+        prm.n_slabs = h->nch_pad / 32;
+        prm.n_tasks = V * prm.n_slabs;
         prm.task_counter = h->task_counter.p;
-        prm.arena_d = h->arena_d.p; prm.arena_t = h->arena_t.p; prm.arena_kcap = h->kcap;
-        prm.arena_stride = h->mh_grid * SSPS_BLOCK;
+        prm.order = h->order.p; prm.vcost = h->vcost.p;
+        prm.big_d = h->big_d.p; prm.big_w = h->big_w.p; prm.big_r = h->big_r.p;
+        prm.x_d = h->x_d.p; prm.x_t = h->x_t.p;
+        prm.kcap = h->kcap; prm.stride = h->mh_grid * SSPS_BLOCK;
         prm.stats = h->stats.p;
         prm.khist = h->cfg.collect_khist ? h->khist.p : nullptr;
         if (log_cp) {
@@ -669,6 +712,15 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
             prm.pev = h->pev.p; prm.pev_n = h->pev_n.p; prm.pev_cap = h->pev_cap;
             prm.lev_val = h->lev_val.p; prm.lev_idx = h->lev_idx.p; prm.lev_n = h->lev_n.p; prm.lev_cap = h->lev_cap;
         }
+        // task order: vertices by the cycles they cost in the previous launch (first launch: by in-degree)
+        if (!h->have_cost) {
+            cost_from_state_kernel<<<V, 128, 0, h->stream>>>(h->st, V, h->vcost.p);
+            CKS(launch_ok(h, "cost_from_state"));
+        }
+        order_kernel<<<div_up((size_t)V, 128), 128, 0, h->stream>>>(h->vcost.p, V, h->order.p);
+        CKS(launch_ok(h, "order"));
+        CK(cudaMemsetAsync(h->vcost.p, 0, h->vcost.bytes(), h->stream));
+        h->have_cost = true;
         CK(cudaMemsetAsync(h->task_counter.p, 0, sizeof(int), h->stream));
         if (ev_used == h->ev_pool.size()) {
             cudaEvent_t a, b;
@@ -678,10 +730,12 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
         CK(cudaEventRecord(h->ev_pool[ev_used].first, h->stream));
         if (replay_host) {
             ReplaySource src{replay_dev.p + (size_t)done * C * V * 6, C, V};
-            mh_sweeps_kernel<ReplaySource><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+            if (h->cfg.verify) mh_sweeps_kernel<ReplaySource, true><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+            else mh_sweeps_kernel<ReplaySource, false><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
         } else {
             PhiloxSource src{h->seed, h->chain_offset};
-            mh_sweeps_kernel<PhiloxSource><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+            if (h->cfg.verify) mh_sweeps_kernel<PhiloxSource, true><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+            else mh_sweeps_kernel<PhiloxSource, false><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
         }
         CKS(launch_ok(h, "mh_sweeps_kernel"));
         CK(cudaEventRecord(h->ev_pool[ev_used].second, h->stream));
@@ -700,7 +754,7 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
     for (size_t e = 0; e < ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
     if (sweeps_done_out) *sweeps_done_out = done;
     unsigned long long overflow = 0;
-    CK(cudaMemcpy(&overflow, h->stats.p + 5, sizeof overflow, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&overflow, h->stats.p + ST_OVERFLOW, sizeof overflow, cudaMemcpyDeviceToHost));
     if (overflow) return fail(SSPS_ERR_INDEGREE, "a parent set exceeded max_indegree=%d; results are invalid, re-create with a larger bound", h->kcap);
     return SSPS_OK;
 }
@@ -761,6 +815,24 @@ int ssps_replay(ssps_handle* h, int64_t n_sweeps, const double* draws, int32_t t
     CKS(bind(h));
     if (!draws) return fail(SSPS_ERR_INVALID, "ssps_replay: null draws");
     return run_sweeps(h, n_sweeps, 0.0, thinning, draws, nullptr);
+}
+
+int ssps_export_draws(ssps_handle* h, int64_t first_sweep, int64_t n_sweeps, double* out) {
+    CKS(bind(h));
+    if (h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "no chains");
+    if (first_sweep < 0 || n_sweeps < 0 || !out) return fail(SSPS_ERR_INVALID, "ssps_export_draws: bad argument");
+    if (n_sweeps == 0) return SSPS_OK;
+    const size_t per = (size_t)h->n_chains * h->V;
+    if ((double)per * (double)n_sweeps * 6.0 * 8.0 > 8e9) return fail(SSPS_ERR_NOMEM, "ssps_export_draws: more than 8 GB requested");
+    const size_t total = per * (size_t)n_sweeps;
+    DevBuf<double> d;
+    CK(d.alloc(total * 6));
+    PhiloxSource src{h->seed, h->chain_offset};
+    export_draws_kernel<<<div_up(total, 256), 256, 0, h->stream>>>(src, h->n_chains, h->V, first_sweep, (int)n_sweeps, d.p);
+    CKS(launch_ok(h, "export_draws"));
+    CKS(download(h, out, d.p, total * 6));
+    CK(cudaStreamSynchronize(h->stream));
+    return SSPS_OK;
 }
 
 int ssps_get_state(ssps_handle* h, int32_t chain, int32_t* indeg, int32_t* members, int64_t cap, int64_t* n_members,
@@ -1012,17 +1084,19 @@ int ssps_get_stats(ssps_handle* h, ssps_run_stats* out) {
     memset(out, 0, sizeof *out);
     out->kernel_launches = h->kernel_launches;
     if (h->n_chains > 0) {
-        unsigned long long st[8];
+        unsigned long long st[ST_N];
         CK(cudaStreamSynchronize(h->stream));
         CK(cudaMemcpy(st, h->stats.p, sizeof st, cudaMemcpyDeviceToHost));
         out->sweeps_done = h->sweeps_done;
         out->samples_recorded = h->samples_recorded;
-        out->n_proposals = (int64_t)st[6];
-        out->n_accepted = (int64_t)st[0];
-        out->n_lambda_accepted = (int64_t)st[1];
-        out->sum_k = (int64_t)st[2];
-        out->algorithmic_flops = (double)st[3] / 3.0;   // sum (k^3 + 6k^2 + 6k) / 3 = sum k^3/3 + 2k^2 + 2k
-        out->algorithmic_bytes = 8.0 * (double)st[4];
+        out->n_proposals = (int64_t)st[ST_PROP];
+        out->n_accepted = (int64_t)st[ST_ACCP];
+        out->n_lambda_accepted = (int64_t)st[ST_ACCL];
+        out->sum_k = (int64_t)st[ST_SUMK];
+        out->algorithmic_flops = (double)st[ST_F3] / 3.0;   // sum (k^3 + 6k^2 + 6k) / 3 = sum k^3/3 + 2k^2 + 2k
+        out->algorithmic_bytes = 8.0 * (double)st[ST_BYTES];
+        out->n_tier1 = (int64_t)st[ST_TIER1]; out->n_big_steps = (int64_t)st[ST_BIG_STEPS];
+        out->n_lambda_exact = (int64_t)st[ST_LAM_EXACT]; out->n_mismatch = (int64_t)st[ST_MISMATCH];
         out->kernel_ms = h->kernel_ms;
         out->mh_launches = h->mh_launches;
     }

@@ -23,9 +23,7 @@
 #include <stdint.h>
 
 #define SSPS_PIVOT_TOL 9.094947017729282e-13  // 2^-40
-#define SSPS_KS 8                               // parent sets up to this size are scored out of shared memory
 #define SSPS_TRI(k) (((k) * ((k) + 1)) / 2)
-#define SSPS_BLOCK 128
 
 enum { ACT_ADD = 1, ACT_SWAP = 2, ACT_REM = 3 };
 
@@ -44,6 +42,11 @@ struct SspsDev {
     const double* mvP;                   // [i][k][3]   k = 0..V : P(add), P(swap), P(remove)
     const double* mvLogP;                // [i][k][3]
     const double* logint;                // log(m), m = 0..V+1
+    // fp32 screening tables for the lambda move (K3): per child the groups with 1-c != 0 as
+    // (-(1-c) log2 e, mult ln 2), and the screening margin of the child
+    const int* fgrp_off;                 // V+1
+    const float2* fgrp;
+    const float* lam_margin;             // V
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -72,38 +75,6 @@ __device__ __forceinline__ double u53_to_unit(uint32_t hi, uint32_t lo) {
     return (double)x * 1.1102230246251565e-16;
 }
 
-struct StepDraws { double z, u_lam, u_act, u_add, u_rem, u_acc; };
-
-struct PhiloxSource {
-    uint64_t seed; uint32_t chain_offset;
-    __device__ __forceinline__ StepDraws get(int chain_local, int vertex, uint64_t sweep, int64_t /*local*/) const {
-        uint32_t a[4], b[4], c[4];
-        uint32_t chain = chain_offset + (uint32_t)chain_local;
-        philox_block(seed, chain, (uint32_t)vertex, sweep, 0, a);
-        philox_block(seed, chain, (uint32_t)vertex, sweep, 1, b);
-        philox_block(seed, chain, (uint32_t)vertex, sweep, 2, c);
-        StepDraws d;
-        double u1 = u32_to_unit(a[0]), u2 = u32_to_unit(a[1]);
-        d.z = sqrt(-2.0 * log(u1)) * cos(6.283185307179586 * u2);
-        d.u_lam = u53_to_unit(a[2], a[3]);
-        d.u_act = u32_to_unit(b[0]);
-        d.u_add = u32_to_unit(b[1]);
-        d.u_rem = u32_to_unit(b[2]);
-        d.u_acc = u53_to_unit(c[0], c[1]);
-        return d;
-    }
-};
-
-struct ReplaySource {
-    const double* draws; int n_chains; int V;   // [local sweep][chain][vertex][6]
-    __device__ __forceinline__ StepDraws get(int chain_local, int vertex, uint64_t /*sweep*/, int64_t local) const {
-        const double* p = draws + ((((size_t)local * n_chains + chain_local) * V) + vertex) * 6;
-        StepDraws d;
-        d.z = p[0]; d.u_lam = p[1]; d.u_act = p[2]; d.u_add = p[3]; d.u_rem = p[4]; d.u_acc = p[5];
-        return d;
-    }
-};
-
 // ------------------------------------------------------------------------------------------------
 // Per-thread scratch: lower-triangular factor (diagonal slot = 1/d), w, and the proposed set,
 // interleaved across threads so that a warp touching the same logical index is conflict-free /
@@ -117,6 +88,7 @@ struct Scratch {
     __device__ __forceinline__ double& L(int e) const { return d[(size_t)e * stride]; }
     __device__ __forceinline__ double& w(int a) const { return d[(size_t)(SSPS_TRI(kcap) + a) * stride]; }
     __device__ __forceinline__ uint16_t& T(int a) const { return t[(size_t)a * stride]; }
+    __device__ __forceinline__ uint16_t& S(int a) const { return t[(size_t)(kcap + a) * stride]; }   // second id list (K3 only)
 };
 
 // lml(child, S') for the sorted set held in sc.T(0..kn-1).  Mirrors orc_lml_chol operation for
@@ -311,8 +283,9 @@ __global__ void score_kernel(SspsDev P, int n_sets, const int* __restrict__ chil
 // chains of the same vertex reads and writes it coalesced:
 //   k      [vertex][chain]            int32
 //   lambda [vertex][chain]            fp64
-//   slots  [vertex][a][chain]         uint32 = parent id | (rel << 16), sorted by id, a < V
-// `rel` is only meaningful inside a launch (lazy tally, see below) and is 0 between launches.
+//   slots  [vertex][a][chain]         uint32 = parent id | (rank << 16), a < V: ARRIVAL order (the order in
+//                                     which the parents joined the set; the initial state arrives sorted),
+//                                     rank = position of the id in the sorted parent list
 // ------------------------------------------------------------------------------------------------
 struct ChainState {
     int n_chains, nch_pad;
@@ -342,226 +315,10 @@ __global__ void init_chains_kernel(SspsDev P, ChainState st, uint64_t seed, uint
         if ((j & 3) == 0) philox_block(seed, cid, (uint32_t)vertex, 0, 1u + (uint32_t)(j >> 2), w);
         const double conf = P.conf[(size_t)j + (size_t)P.V * vertex];
         const double p = enl / (enl + exp(-conf * lam));
-        if (u32_to_unit(w[j & 3]) < p) { slot_ref(st, P.V, vertex, k, chain) = (uint32_t)j; ++k; }
+        if (u32_to_unit(w[j & 3]) < p) { slot_ref(st, P.V, vertex, k, chain) = (uint32_t)j | ((uint32_t)k << 16); ++k; }
     }
     st.k[(size_t)vertex * st.nch_pad + chain] = k;
     st.lambda[(size_t)vertex * st.nch_pad + chain] = lam;
-}
-
-// ------------------------------------------------------------------------------------------------
-// K3: the persistent fused MH kernel.
-//
-// Work unit = one warp-task = (vertex i, slab of 32 chains): lane = chain, so the 32 micro-chains
-// of a warp share r_i, the prior column, the move table row and (statistically) the in-degree
-// distribution.  Warps pull tasks from an atomic counter; each task runs ALL `n_local` sweeps of
-// this launch for its 32 micro-chains (the posterior factorises over vertices,
-// dbn_models.jl:94-96, so micro-chains never communicate).
-//
-// Per sweep and micro-chain: lambda move, parent-set move (add / swap / remove), both with their
-// own accept test, then thinned recording.  Edge tallies are LAZY: a parent's slot remembers the
-// first recorded sample that saw it (`rel`), and the tally is credited when the parent leaves
-// the set or when the launch ends -- one global read-modify-write per ACCEPTED move instead of
-// |S| per recorded sample.
-// ------------------------------------------------------------------------------------------------
-struct MhParams {
-    int64_t sweep0;          // sweeps already done (multiple of thinning)
-    int n_local;             // sweeps in this launch
-    int thinning;
-    int n_tasks;
-    int* task_counter;
-    // global scratch arena for |S'| > SSPS_KS, per resident thread
-    double* arena_d; uint16_t* arena_t; int arena_kcap; int arena_stride;
-    // stats: [0] accepted parent moves, [1] accepted lambda moves, [2] sum k, [3] sum (k^3+6k^2+6k),
-    //        [4] sum (k(k+1)/2 + k), [5] overflow flag, [6] proposals
-    unsigned long long* stats;
-    unsigned long long* khist;   // nullable, 64 bins
-    // change-point log (nullable): per micro-chain mc = chain*V + vertex
-    uint32_t* pev; int* pev_n; int pev_cap;        // parent events: id | rel_rec<<16 | flag<<31
-    double* lev_val; uint16_t* lev_idx; int* lev_n; int lev_cap;
-};
-
-__device__ __forceinline__ int ceil_div_i(int a, int b) { return (a + b - 1) / b; }
-
-template <class Source>
-__global__ void __launch_bounds__(SSPS_BLOCK) mh_sweeps_kernel(SspsDev P, ChainState st, MhParams prm, Source src) {
-    extern __shared__ double smem_d[];
-    const int lane = threadIdx.x & 31;
-    const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
-    Scratch ssm{smem_d + threadIdx.x, (uint16_t*)(smem_d + (size_t)(SSPS_TRI(SSPS_KS) + SSPS_KS) * blockDim.x) + threadIdx.x,
-                (int)blockDim.x, SSPS_KS};
-    Scratch sgl{prm.arena_d + gtid, prm.arena_t + gtid, prm.arena_stride, prm.arena_kcap};
-    const int V = P.V;
-    const int thin = prm.thinning;
-
-    unsigned long long s_accp = 0, s_accl = 0, s_k = 0, s_f3 = 0, s_b = 0, s_prop = 0;
-    bool overflow = false;
-
-    for (;;) {
-        int task = 0;
-        if (lane == 0) task = atomicAdd(prm.task_counter, 1);
-        task = __shfl_sync(0xffffffffu, task, 0);
-        if (task >= prm.n_tasks) break;
-        const int i = task % V;
-        const int chain = (task / V) * 32 + lane;
-        if (chain < st.n_chains) {
-            const size_t sidx = (size_t)i * st.nch_pad + chain;
-            const size_t mc = (size_t)chain * V + i;
-            int k = st.k[sidx];
-            double lam = st.lambda[sidx];
-            const double* __restrict__ omc_i = P.omc + (size_t)V * i;
-            uint32_t* __restrict__ cnt_row = st.counts + mc * V;
-
-            // cached pure functions of the state
-            double nrm = prior_normaliser(P, i, lam);
-            double somc = 0.0;
-            for (int a = 0; a < k; ++a) somc += __ldg(omc_i + (slot_ref(st, V, i, a, chain) & 0xffffu));
-            double lml;
-            {
-                const Scratch& sc = (k <= SSPS_KS) ? ssm : sgl;
-                if (k > sgl.kcap) { overflow = true; lml = 0.0; }
-                else {
-                    for (int a = 0; a < k; ++a) sc.T(a) = (uint16_t)(slot_ref(st, V, i, a, chain) & 0xffffu);
-                    lml = score_set(P, i, sc, k, nullptr);
-                }
-            }
-            double lam_sum = 0.0, lam_sq = 0.0, lam_logged = lam;
-            int n_pev = 0, n_lev = 0;
-
-            for (int l = 1; l <= prm.n_local; ++l) {
-                const StepDraws d = src.get(chain, i, (uint64_t)(prm.sweep0 + l), (int64_t)(l - 1));
-
-                // ---------------- lambda move ----------------
-                const double lam_new = lam + P.sigma * d.z;
-                if (lam_new >= P.lambda_min && lam_new <= P.lambda_max) {
-                    const double nrm_new = prior_normaliser(P, i, lam_new);
-                    const double w = -(lam_new - lam) * somc - (nrm_new - nrm);
-                    if (log(d.u_lam) < w) { lam = lam_new; nrm = nrm_new; ++s_accl; }
-                }
-
-                // ---------------- parent-set move ----------------
-                const double* __restrict__ mvP = P.mvP + ((size_t)i * (V + 1) + k) * 3;
-                const double* __restrict__ mvL = P.mvLogP + ((size_t)i * (V + 1) + k) * 3;
-                const double p_add = __ldg(mvP), p_swp = __ldg(mvP + 1);
-                const double cp2 = p_add + p_swp;
-                const int action = d.u_act < p_add ? ACT_ADD : (d.u_act < cp2 ? ACT_SWAP : ACT_REM);
-                int j_add = -1, j_rem = -1, pos_rem = -1;
-                if (action != ACT_REM) {
-                    const int m = V - k;
-                    int a = 1 + (int)floor(d.u_add * (double)m); if (a > m) a = m;
-                    int p = 0;
-                    while (p < k) { if ((int)(slot_ref(st, V, i, p, chain) & 0xffffu) - p >= a) break; ++p; }
-                    j_add = a + p - 1;
-                }
-                if (action != ACT_ADD) {
-                    int r = 1 + (int)floor(d.u_rem * (double)k); if (r > k) r = k;
-                    pos_rem = r - 1;
-                    j_rem = (int)(slot_ref(st, V, i, pos_rem, chain) & 0xffffu);
-                }
-                const int kn = k + (action == ACT_ADD) - (action == ACT_REM);
-                double fwd = 0.0, bwd = 0.0;
-                if (action == ACT_ADD) {
-                    fwd = __ldg(mvL) - __ldg(P.logint + (V - k));
-                    bwd = __ldg(P.mvLogP + ((size_t)i * (V + 1) + (k + 1)) * 3 + 2) - __ldg(P.logint + (k + 1));
-                } else if (action == ACT_REM) {
-                    fwd = __ldg(mvL + 2) - __ldg(P.logint + k);
-                    bwd = __ldg(P.mvLogP + ((size_t)i * (V + 1) + (k - 1)) * 3 + 0) - __ldg(P.logint + (V - k + 1));
-                }
-                ++s_prop;
-                s_k += (unsigned long long)kn;
-                s_f3 += (unsigned long long)kn * kn * kn + 6ull * kn * kn + 6ull * kn;
-                s_b += (unsigned long long)(kn * (kn + 1) / 2 + kn);
-                if (prm.khist) atomicAdd(prm.khist + (kn < 63 ? kn : 63), 1ull);
-
-                double lml_new;
-                if (kn > sgl.kcap) { overflow = true; lml_new = __longlong_as_double(0x7ff8000000000000LL); }
-                else {
-                    const Scratch& sc = (kn <= SSPS_KS) ? ssm : sgl;
-                    // proposed sorted set: current slots minus j_rem plus j_add
-                    int t = 0; bool placed = (j_add < 0);
-                    for (int a = 0; a < k; ++a) {
-                        const int id = (int)(slot_ref(st, V, i, a, chain) & 0xffffu);
-                        if (a == pos_rem) continue;
-                        if (!placed && j_add < id) { sc.T(t++) = (uint16_t)j_add; placed = true; }
-                        sc.T(t++) = (uint16_t)id;
-                    }
-                    if (!placed) sc.T(t++) = (uint16_t)j_add;
-                    lml_new = score_set(P, i, sc, kn, nullptr);
-                }
-                double dprior = 0.0;
-                if (j_add >= 0) dprior = -lam * __ldg(omc_i + j_add);
-                if (j_rem >= 0) dprior = dprior + lam * __ldg(omc_i + j_rem);
-                const double w = dprior + (lml_new - lml);
-                const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
-                if (log(d.u_acc) < alpha) {
-                    ++s_accp;
-                    const int rel_now = ceil_div_i(l, thin) - 1;   // recorded samples of this launch that precede the change
-                    if (j_rem >= 0) {
-                        const uint32_t sl = slot_ref(st, V, i, pos_rem, chain);
-                        const int credit = rel_now - (int)(sl >> 16);
-                        if (credit > 0) cnt_row[j_rem] += (uint32_t)credit;
-                        for (int a = pos_rem; a < k - 1; ++a) slot_ref(st, V, i, a, chain) = slot_ref(st, V, i, a + 1, chain);
-                        --k;
-                        if (prm.pev && n_pev < prm.pev_cap)
-                            prm.pev[mc * prm.pev_cap + n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
-                    }
-                    if (j_add >= 0) {
-                        int a = k;
-                        while (a > 0) {
-                            const uint32_t sl = slot_ref(st, V, i, a - 1, chain);
-                            if ((int)(sl & 0xffffu) < j_add) break;
-                            slot_ref(st, V, i, a, chain) = sl; --a;
-                        }
-                        slot_ref(st, V, i, a, chain) = (uint32_t)j_add | ((uint32_t)rel_now << 16);
-                        ++k;
-                        if (prm.pev && n_pev < prm.pev_cap)
-                            prm.pev[mc * prm.pev_cap + n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
-                    }
-                    lml = lml_new;
-                    somc = 0.0;
-                    for (int a = 0; a < k; ++a) somc += __ldg(omc_i + (slot_ref(st, V, i, a, chain) & 0xffffu));
-                }
-
-                // ---------------- thinned recording ----------------
-                if (l % thin == 0) {
-                    lam_sum += lam; lam_sq = fma(lam, lam, lam_sq);
-                    if (prm.lev_val && lam != lam_logged) {
-                        if (n_lev < prm.lev_cap) {
-                            prm.lev_val[mc * prm.lev_cap + n_lev] = lam;
-                            prm.lev_idx[mc * prm.lev_cap + n_lev] = (uint16_t)(l / thin);
-                            ++n_lev;
-                        }
-                        lam_logged = lam;
-                    }
-                }
-            }
-
-            // flush lazy tallies, reset rel, store state
-            const int rec_local = prm.n_local / thin;
-            for (int a = 0; a < k; ++a) {
-                uint32_t& sl = slot_ref(st, V, i, a, chain);
-                const int credit = rec_local - (int)(sl >> 16);
-                if (credit > 0) cnt_row[sl & 0xffffu] += (uint32_t)credit;
-                sl &= 0xffffu;
-            }
-            st.k[sidx] = k;
-            st.lambda[sidx] = lam;
-            st.lam_sum[mc] += lam_sum;
-            st.lam_sq[mc] += lam_sq;
-            if (prm.pev_n) prm.pev_n[mc] = n_pev;
-            if (prm.lev_n) prm.lev_n[mc] = n_lev;
-        }
-        __syncwarp();
-    }
-
-    // stats: warp reduce, one atomic per warp
-    unsigned long long v[6] = {s_accp, s_accl, s_k, s_f3, s_b, s_prop};
-#pragma unroll
-    for (int e = 0; e < 6; ++e) {
-        unsigned long long x = v[e];
-        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-        if (lane == 0 && x) atomicAdd(prm.stats + (e < 5 ? e : 6), x);
-    }
-    if (overflow) atomicExch(prm.stats + 5, 1ull);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -574,7 +331,10 @@ __global__ void export_chain_kernel(SspsDev P, ChainState st, int chain, int* __
     const size_t sidx = (size_t)i * st.nch_pad + chain;
     const int k = st.k[sidx];
     indeg[i] = k; lambda[i] = st.lambda[sidx];
-    for (int a = 0; a < k; ++a) members_padded[(size_t)i * P.V + a] = (int)(slot_ref(st, P.V, i, a, chain) & 0xffffu);
+    for (int a = 0; a < k; ++a) {       // slots are in arrival order; the word carries the sorted rank
+        const uint32_t sl = slot_ref(st, P.V, i, a, chain);
+        members_padded[(size_t)i * P.V + (sl >> 16)] = (int)(sl & 0xffffu);
+    }
 }
 
 __global__ void import_state_kernel(SspsDev P, ChainState st, const int* __restrict__ offsets,
@@ -584,7 +344,7 @@ __global__ void import_state_kernel(SspsDev P, ChainState st, const int* __restr
     if (vertex >= P.V || chain >= st.n_chains) return;
     const size_t mc = (size_t)chain * P.V + vertex;
     const int k = offsets[mc + 1] - offsets[mc];
-    for (int a = 0; a < k; ++a) slot_ref(st, P.V, vertex, a, chain) = (uint32_t)members[offsets[mc] + a];
+    for (int a = 0; a < k; ++a) slot_ref(st, P.V, vertex, a, chain) = (uint32_t)members[offsets[mc] + a] | ((uint32_t)a << 16);
     st.k[(size_t)vertex * st.nch_pad + chain] = k;
     st.lambda[(size_t)vertex * st.nch_pad + chain] = lambda[mc];
 }

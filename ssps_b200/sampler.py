@@ -62,7 +62,8 @@ class Sampler:
 
     def __init__(self, device: int = -1, regression_deg: int = 1, large_indeg: float = 20.0,
                  lambda_max: float = 15.0, lambda_prop_std: float = 0.25, max_indegree: int = 0,
-                 psrf_grid: int = 0, record_changepoints: bool = False, collect_khist: bool = False):
+                 psrf_grid: int = 0, record_changepoints: bool = False, collect_khist: bool = False,
+                 verify: bool = False):
         self._L = _lib.load()
         cfg = Config()
         cfg.struct_size = C.sizeof(Config)
@@ -75,6 +76,7 @@ class Sampler:
         cfg.psrf_grid = psrf_grid
         cfg.record_changepoints = int(record_changepoints)
         cfg.collect_khist = int(collect_khist)
+        cfg.verify = int(verify)
         self._h = C.c_void_p()
         check(self._L.ssps_create(C.byref(cfg), C.byref(self._h)))
         self.cfg = cfg
@@ -187,6 +189,13 @@ class Sampler:
         if d.ndim != 4 or d.shape[1:] != (self.n_chains, self.V, 6):
             raise ValueError("draws must be (n_sweeps, %d, %d, 6)" % (self.n_chains, self.V))
         check(self._L.ssps_replay(self._h, d.shape[0], _d(d), int(thinning)))
+
+    def export_draws(self, first_sweep: int, n_sweeps: int) -> np.ndarray:
+        """The (z, u_lam, u_act, u_add, u_rem, u_acc) numbers update_loop uses for sweeps
+        first_sweep+1 .. first_sweep+n_sweeps, shaped like replay()'s input."""
+        out = np.empty((n_sweeps, self.n_chains, self.V, 6))
+        check(self._L.ssps_export_draws(self._h, int(first_sweep), int(n_sweeps), _d(out)))
+        return out
 
     def state(self, chain: int, want_lml: bool = True):
         V = self.V

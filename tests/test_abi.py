@@ -19,20 +19,20 @@ def test_header_symbols_are_exported_and_bound():
     from ssps_b200 import _lib
     L = _lib.load()
     names = _declared()
-    assert len(names) >= 28
+    assert len(names) >= 29
     raw = ctypes.CDLL(_lib.lib_path())
     for n in names:
         assert hasattr(raw, n), "library does not export %s" % n
         assert n in _lib.SIGNATURES, "binding misses %s" % n
     assert set(_lib.SIGNATURES) == set(names)
-    assert L.ssps_abi_version() == 1
+    assert L.ssps_abi_version() == 2
     assert L.ssps_psrf_sums_len(10) == 3 * 100 + 30 + 2
 
 
 def test_struct_layouts_match_header():
     from ssps_b200 import _lib
     assert ctypes.sizeof(_lib.Config) == 56
-    assert ctypes.sizeof(_lib.RunStats) == 88
+    assert ctypes.sizeof(_lib.RunStats) == 88 + 4 * 8
 
 
 def test_no_cpu_fallback_without_gpu():

@@ -1,0 +1,27 @@
+"""GPU diagnostic: tier statistics and throughput of the MH kernel on the bench workload."""
+import sys, time, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+from bench import make_workload
+from ssps_b200 import Sampler
+
+V = int(sys.argv[1]) if len(sys.argv) > 1 else 100
+C = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+S = int(sys.argv[3]) if len(sys.argv) > 3 else 400
+verify = len(sys.argv) > 4 and sys.argv[4] == "verify"
+T = int(os.environ.get("DIAG_T", "8"))
+ds, xm, xp = make_workload(V, T, 4)
+with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), verify=verify) as s:
+    s.set_data(xm, xp, ds.prior_graph)
+    s.generate(C, seed=1)
+    prev = s.stats()
+    for rep in range(4):
+        s.update_loop(S)
+        st = s.stats()
+        dp = st.n_proposals - prev.n_proposals
+        dms = st.kernel_ms - prev.kernel_ms
+        print("rep %d: %.3e prop/s kernel | t1 %.2e big %.2e lamx %.2e (per proposal) acc %.3f lam_acc %.3f mism %d"
+              % (rep, dp / (dms * 1e-3), (st.n_tier1 - prev.n_tier1) / dp, (st.n_big_steps - prev.n_big_steps) / dp,
+                 (st.n_lambda_exact - prev.n_lambda_exact) / dp, (st.n_accepted - prev.n_accepted) / dp,
+                 (st.n_lambda_accepted - prev.n_lambda_accepted) / dp, st.n_mismatch))
+        prev = st
