@@ -470,6 +470,7 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     h->nch_pad = ((n_chains + 31) / 32) * 32;
     int kcap = h->cfg.max_indegree > 0 ? h->cfg.max_indegree : std::min(V, 64);
     h->kcap = std::min(kcap, V);
+    if (h->kcap > 128) return fail(SSPS_ERR_UNSUPPORTED, "max_indegree=%d: the per-thread factor arena supports at most 128", h->kcap);
     CK(h->k.alloc((size_t)V * h->nch_pad)); CK(h->lambda.alloc((size_t)V * h->nch_pad));
     CK(h->slots.alloc(vv * h->nch_pad));
     CK(h->counts.alloc(vv * n_chains));

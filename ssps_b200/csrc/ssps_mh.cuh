@@ -155,16 +155,16 @@ struct BigAcc {     // global arena, element-major over all resident threads: [e
     double* d; uint32_t* w; uint16_t* r; int stride, kcap;
     static constexpr bool is_small = false;
     __device__ __forceinline__ int cap() const { return kcap; }
-    __device__ __forceinline__ double& D(int e) const { return d[(size_t)e * stride]; }
-    __device__ __forceinline__ double& Lo(int a, int b) const { return d[(size_t)(SSPS_TRI(a) + b) * stride]; }
-    __device__ __forceinline__ double& Li(int a) const { return d[(size_t)(SSPS_TRI(a) + a) * stride]; }
-    __device__ __forceinline__ double& Wv(int a) const { return d[(size_t)(SSPS_TRI(kcap) + a) * stride]; }
-    __device__ __forceinline__ double& So(int a, int b) const { return d[(size_t)(SSPS_ROWLEN(kcap) + SSPS_TRI(a) + b) * stride]; }
-    __device__ __forceinline__ double& Si(int a) const { return d[(size_t)(SSPS_ROWLEN(kcap) + SSPS_TRI(a) + a) * stride]; }
-    __device__ __forceinline__ double& Sw(int a) const { return d[(size_t)(SSPS_ROWLEN(kcap) + SSPS_TRI(kcap) + a) * stride]; }
-    __device__ __forceinline__ uint32_t& W(int a) const { return w[(size_t)a * stride]; }
-    __device__ __forceinline__ int rank(int a) const { return (int)r[(size_t)a * stride]; }
-    __device__ __forceinline__ void set_rank(int a, int v) const { r[(size_t)a * stride] = (uint16_t)v; }
+    __device__ __forceinline__ double& D(int e) const { return d[(unsigned)e * (unsigned)stride]; }
+    __device__ __forceinline__ double& Lo(int a, int b) const { return d[(unsigned)(SSPS_TRI(a) + b) * (unsigned)stride]; }
+    __device__ __forceinline__ double& Li(int a) const { return d[(unsigned)(SSPS_TRI(a) + a) * (unsigned)stride]; }
+    __device__ __forceinline__ double& Wv(int a) const { return d[(unsigned)(SSPS_TRI(kcap) + a) * (unsigned)stride]; }
+    __device__ __forceinline__ double& So(int a, int b) const { return d[(unsigned)(SSPS_ROWLEN(kcap) + SSPS_TRI(a) + b) * (unsigned)stride]; }
+    __device__ __forceinline__ double& Si(int a) const { return d[(unsigned)(SSPS_ROWLEN(kcap) + SSPS_TRI(a) + a) * (unsigned)stride]; }
+    __device__ __forceinline__ double& Sw(int a) const { return d[(unsigned)(SSPS_ROWLEN(kcap) + SSPS_TRI(kcap) + a) * (unsigned)stride]; }
+    __device__ __forceinline__ uint32_t& W(int a) const { return w[(unsigned)a * (unsigned)stride]; }
+    __device__ __forceinline__ int rank(int a) const { return (int)r[(unsigned)a * (unsigned)stride]; }
+    __device__ __forceinline__ void set_rank(int a, int v) const { r[(unsigned)a * (unsigned)stride] = (uint16_t)v; }
 };
 
 struct Lane {
@@ -216,7 +216,7 @@ __device__ __forceinline__ double normaliser_fast(const SspsDev& P, int child, d
 
 // lambda move in the reference order (the oracle's chain_step restates exactly this); xs.S(0..k-1)
 // holds the SORTED current set
-__device__ __noinline__ int lambda_exact_decide(const SspsDev P, const int child, const Scratch xs, const int k, const double lam,
+__device__ __noinline__ int lambda_exact_decide(const SspsDev& P, const int child, const Scratch& xs, const int k, const double lam,
                                                 const double lam_new, const double u_lam) {
     const double* __restrict__ omc_i = P.omc + (size_t)P.V * child;
     double somc = 0.0;
@@ -226,7 +226,7 @@ __device__ __noinline__ int lambda_exact_decide(const SspsDev P, const int child
     return log(u_lam) < w ? 1 : 0;
 }
 
-__device__ __noinline__ void write_sorted(const int mode, const SmallAcc S, const BigAcc B, const Scratch xs, const int k) {
+__device__ __noinline__ void write_sorted(const int mode, const SmallAcc& S, const BigAcc& B, const Scratch& xs, const int k) {
     if (mode == MODE_SMALL) { for (int b = 0; b < k; ++b) xs.S(S.rank(b)) = (uint16_t)(S.W(b) & 0xffffu); }
     else { for (int b = 0; b < k; ++b) xs.S(B.rank(b)) = (uint16_t)(B.W(b) & 0xffffu); }
 }
@@ -362,7 +362,7 @@ __device__ __forceinline__ double build_factor(const SspsDev& P, const double* _
 }
 
 // ids (word, rank) of the lane are in the arena; build its factor in the tier its size selects
-__device__ __noinline__ Lane lane_settle(const SspsDev P, const int child, Lane L, const SmallAcc S, const KCtx C) {
+__device__ __noinline__ Lane lane_settle(const SspsDev& P, const int child, Lane L, const SmallAcc& S, const KCtx& C) {
     const int k = L.k;
     const double* __restrict__ omc_i = P.omc + (size_t)P.V * child;
     const double* __restrict__ Ri = P.R + (size_t)P.V * child;
@@ -382,7 +382,7 @@ __device__ __noinline__ Lane lane_settle(const SspsDev P, const int child, Lane 
 }
 
 // a SMALL lane accepted a move that outgrows shared memory: hand ids over to the arena, rebuild there
-__device__ __noinline__ Lane small_to_big(const SspsDev P, const int child, Lane L, const SmallAcc S, const KCtx C, const int p,
+__device__ __noinline__ Lane small_to_big(const SspsDev& P, const int child, Lane L, const SmallAcc& S, const KCtx& C, const int p,
                                           const int j_add, const int j_rem, const int rel_now) {
     const int k = L.k;
     for (int b = 0; b < k; ++b) { C.big.W(b) = S.W(b); C.big.set_rank(b, S.rank(b)); }
@@ -490,9 +490,232 @@ __device__ __forceinline__ int parent_move(const SspsDev& P, const int child, co
     return 1;
 }
 
+// ------------------------------------------------------------------------------------------------
+// The parent-set move of a SMALL lane (|S| <= SSPS_KS): same arithmetic as parent_move<SmallAcc>,
+// but statically unrolled over SSPS_KS slots with the proposed set's factor held in REGISTERS, so
+// that the 32 lanes of a warp (different k, different removal position p) walk one instruction
+// stream: rows/entries a lane does not need are predicated off, rows nobody needs are skipped by a
+// warp-uniform branch.  NL(a, b) = entry (a, b) of the factor in the PROPOSED set's coordinates
+// (arrival positions after the removal): rows < p and the entries < p of later rows are the
+// cached values, the rest is recomputed; the appended parent's row is jl[].
+// ------------------------------------------------------------------------------------------------
+#define NL(a, b) nl[SSPS_TRI(a) - (a) + (b)]       // strictly lower triangle: row a starts at a(a-1)/2
+
+template <bool VERIFY>
+__device__ __forceinline__ int small_move(const SspsDev& P, const int child, const StepDraws& d, Lane& L, const SmallAcc& S,
+                                          const KCtx& C, const int rel_now, unsigned& n_t1, int& kn_out) {
+    constexpr int KS = SSPS_KS;
+    const int V = P.V, k = L.k;
+    const size_t trow = ((size_t)child * (V + 1) + k) * 3;
+    const double p_add = __ldg(P.mvP + trow), p_swp = __ldg(P.mvP + trow + 1);
+    const int action = d.u_act < p_add ? ACT_ADD : (d.u_act < p_add + p_swp ? ACT_SWAP : ACT_REM);
+    const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
+
+    uint32_t idw[KS]; int rk[KS];
+#pragma unroll
+    for (int b = 0; b < KS; ++b) {
+        idw[b] = 0xffffu; rk[b] = -1;
+        if (b < k) { idw[b] = S.W(b); rk[b] = S.rank(b); }
+    }
+    int j_add = -1, j_rem = -1, p = k, rp = 1 << 20;
+    if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
+        const int m = V - k;
+        int a = 1 + (int)floor(d.u_add * (double)m); if (a > m) a = m;
+        int c = 0;
+#pragma unroll
+        for (int b = 0; b < KS; ++b) c += (b < k && (int)(idw[b] & 0xffffu) - rk[b] < a) ? 1 : 0;
+        j_add = a - 1 + c;
+    }
+    if (has_rem) {          // the r-th element of the sorted list
+        int r = 1 + (int)floor(d.u_rem * (double)k); if (r > k) r = k;
+        rp = r - 1;
+#pragma unroll
+        for (int b = 0; b < KS; ++b) if (rk[b] == rp) { p = b; j_rem = (int)(idw[b] & 0xffffu); }
+    }
+    const int kr = k - (has_rem ? 1 : 0);
+    const int kn = kr + (has_add ? 1 : 0);
+    kn_out = kn;
+    double fwd = 0.0, bwd = 0.0;
+    if (action == ACT_ADD) {
+        fwd = __ldg(P.mvLogP + trow) - __ldg(P.logint + (V - k));
+        bwd = __ldg(P.mvLogP + ((size_t)child * (V + 1) + (k + 1)) * 3 + 2) - __ldg(P.logint + (k + 1));
+    } else if (action == ACT_REM) {
+        fwd = __ldg(P.mvLogP + trow + 2) - __ldg(P.logint + k);
+        bwd = __ldg(P.mvLogP + ((size_t)child * (V + 1) + (k - 1)) * 3 + 0) - __ldg(P.logint + (V - k + 1));
+    }
+    if (kn > C.kcap) { atomicExch(C.stats + ST_OVERFLOW, 1ull); return 0; }
+    const double* __restrict__ omc_i = P.omc + (size_t)V * child;
+    const double* __restrict__ Ri = P.R + (size_t)V * child;
+    double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
+    if (has_add) { omc_add = __ldg(omc_i + j_add); dprior = -L.lam * omc_add; }
+    if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
+
+    // ids of the reduced set in its own arrival coordinates (a valid dummy id beyond kr keeps gathers in range)
+    const int dummy = has_add ? j_add : 0;
+    int nid[KS];
+#pragma unroll
+    for (int a = 0; a < KS; ++a) {
+        const int ida = (int)(idw[a] & 0xffffu);
+        const int idn = (a + 1 < KS) ? (int)(idw[(a + 1 < KS) ? a + 1 : a] & 0xffffu) : dummy;
+        nid[a] = (a < kr) ? ((a >= p) ? idn : ida) : dummy;
+    }
+
+    // the cached factor in the reduced set's coordinates; entries to recompute start as 0
+    double nl[SSPS_TRI(KS) - KS + 1], ninv[KS], nw[KS];
+    const int kr_max = __reduce_max_sync(__activemask(), kr);
+    const int p_min = __reduce_min_sync(__activemask(), p);
+#pragma unroll
+    for (int a = 0; a < KS; ++a) {
+        ninv[a] = 0.0; nw[a] = 0.0;
+#pragma unroll
+        for (int m = 0; m < a; ++m) NL(a, m) = 0.0;
+        if (a < kr_max) {
+            if (a < kr) {
+                if (a < p) {
+                    ninv[a] = S.Li(a); nw[a] = S.Wv(a);
+#pragma unroll
+                    for (int m = 0; m < a; ++m) NL(a, m) = S.Lo(a, m);
+                } else if (a + 1 < KS) {
+#pragma unroll
+                    for (int m = 0; m < a; ++m) if (m < p) NL(a, m) = S.Lo(a + 1, m);
+                }
+            }
+        }
+    }
+
+    // rows [p, kr) of the reduced set: recomputed exactly as a from-scratch factorisation would
+#pragma unroll
+    for (int a = 0; a < KS - 1; ++a) {
+        if (a >= p_min && a < kr_max) {
+            if (a >= p && a < kr) {
+                const double* __restrict__ Ga = P.G + (size_t)nid[a] * V;
+                const double gaa = __ldg(Ga + nid[a]);
+                double d2 = gaa, t = __ldg(Ri + nid[a]);
+#pragma unroll
+                for (int b = 0; b < a; ++b) {
+                    double s = __ldg(Ga + nid[b]);
+#pragma unroll
+                    for (int m = 0; m < b; ++m) s = fma(-NL(a, m), NL(b, m), s);
+                    const double l = (b >= p) ? s * ninv[b] : NL(a, b);
+                    NL(a, b) = l;
+                    d2 = fma(-l, l, d2);
+                    t = fma(-l, nw[b], t);
+                }
+                if (d2 > SSPS_PIVOT_TOL * gaa) {
+                    const double invd = 1.0 / sqrt(d2);
+                    ninv[a] = invd; nw[a] = t * invd;
+                } else if (d2 != d2 || gaa != gaa) {
+                    ninv[a] = __longlong_as_double(0x7ff8000000000000LL); nw[a] = ninv[a];
+                } else { ninv[a] = 0.0; nw[a] = 0.0; }
+            }
+        }
+    }
+    double q_new = 0.0;
+#pragma unroll
+    for (int m = 0; m < KS; ++m) if (m < kr) q_new = fma(nw[m], nw[m], q_new);
+
+    // the appended parent's row
+    double jl[KS], jinv = 0.0, jw = 0.0;
+#pragma unroll
+    for (int b = 0; b < KS; ++b) jl[b] = 0.0;
+    if (has_add) {
+        const double* __restrict__ Gj = P.G + (size_t)j_add * V;
+        const double gjj = __ldg(Gj + j_add);
+        double d2 = gjj, t = __ldg(Ri + j_add);
+#pragma unroll
+        for (int b = 0; b < KS; ++b) {
+            if (b < kr_max) {
+                double s = __ldg(Gj + nid[b]);
+#pragma unroll
+                for (int m = 0; m < b; ++m) s = fma(-jl[m], NL(b, m), s);
+                const double l = (b < kr) ? s * ninv[b] : 0.0;
+                jl[b] = l;
+                if (b < kr) { d2 = fma(-l, l, d2); t = fma(-l, nw[b], t); }
+            }
+        }
+        if (d2 > SSPS_PIVOT_TOL * gjj) {
+            jinv = 1.0 / sqrt(d2); jw = t * jinv;
+            q_new = fma(jw, jw, q_new);
+        } else if (d2 != d2 || gjj != gjj) {
+            jinv = __longlong_as_double(0x7ff8000000000000LL); jw = jinv; q_new = jinv;
+        }
+    }
+    const double ip_new = __ldg(P.yty + child) - P.shrink * q_new;
+
+    // ---- screened acceptance test: accept iff log(u) < alpha ----
+    const float lgu = fast_lg2((float)d.u_acc);
+    const float lg_new = fast_lg2((float)ip_new);
+    const double hn = 0.5 * P.dn;
+    const double base = ((dprior - fwd) + bwd) - 0.5 * (double)(kn - k) * P.log1pn;
+    const double diff = SSPS_LN2 * ((double)lgu + hn * ((double)lg_new - (double)L.lg_ip)) - base;
+    const double marg = 1.2e-6 * ((double)fabsf(lgu) + 1.0 + hn * ((double)(fabsf(lg_new) + fabsf(L.lg_ip)) + 2.0)) + 1e-9 * fabs(base) + 1e-6;
+    bool accept = diff < 0.0;
+    if (!(d.u_acc > 1e-30 && fabs(diff) > marg)) {        // too close (or NaN): the reference-order fp64 test
+        ++n_t1;
+        const double lml_cur = -0.5 * (double)k * P.log1pn - 0.5 * P.dn * log(L.ip);
+        const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
+        const double w = dprior + (lml_new - lml_cur);
+        const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
+        accept = log(d.u_acc) < alpha;
+    }
+    if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
+        int t = 0;
+#pragma unroll
+        for (int b = 0; b < KS; ++b) if (b < k && b != p) C.xs.T(t++) = (uint16_t)(idw[b] & 0xffffu);
+        if (j_add >= 0) C.xs.T(t++) = (uint16_t)j_add;
+        const double lml_ref = score_set(P, child, C.xs, t, nullptr);
+        const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
+        if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
+    }
+    if (!accept) return 0;
+
+    if (kn > KS) {      // outgrows shared memory
+        L = small_to_big(P, child, L, S, C, p, j_add, j_rem, rel_now);
+        return 1;
+    }
+    // ---- accepted: tallies / change points, then factor and id list back to shared memory ----
+    if (has_rem) {
+        const int credit = rel_now - (int)(S.W(p) >> 16);
+        if (credit > 0) C.cnt_row[j_rem] += (uint32_t)credit;
+        if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
+    }
+    if (has_add && C.pev && L.n_pev < C.pev_cap)
+        C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
+    int rj = 0;
+#pragma unroll
+    for (int a = 0; a < KS; ++a) {
+        if (a < kr) {
+            // slot a of the reduced set = old slot a (a < p) or a + 1
+            const uint32_t w_old = (a >= p && a + 1 < KS) ? idw[(a + 1 < KS) ? a + 1 : a] : idw[a];
+            int r_old = (a >= p && a + 1 < KS) ? rk[(a + 1 < KS) ? a + 1 : a] : rk[a];
+            r_old -= (r_old > rp) ? 1 : 0;
+            if (has_add) { if ((int)(w_old & 0xffffu) < j_add) ++rj; else ++r_old; }
+            if (a >= p) {
+                S.W(a) = w_old;
+                S.Li(a) = ninv[a]; S.Wv(a) = nw[a];
+#pragma unroll
+                for (int m = 0; m < a; ++m) S.Lo(a, m) = NL(a, m);
+            }
+            S.set_rank(a, r_old);
+        }
+    }
+    if (has_add) {      // row kr (dynamic position)
+#pragma unroll
+        for (int m = 0; m < KS; ++m) if (m < kr) S.Lo(kr, m) = jl[m];
+        S.Li(kr) = jinv; S.Wv(kr) = jw;
+        S.W(kr) = (uint32_t)j_add | ((uint32_t)rel_now << 16);
+        S.set_rank(kr, rj);
+    }
+    L.k = kn;
+    L.somc = (L.somc - omc_rem) + omc_add;
+    L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
+    return 1;
+}
+#undef NL
+
 // lanes whose set lives in the arena
 template <bool VERIFY>
-__device__ __noinline__ Lane big_move(const SspsDev P, const int child, const StepDraws d, Lane L, const SmallAcc S, const KCtx C,
+__device__ __noinline__ Lane big_move(const SspsDev& P, const int child, const StepDraws& d, Lane L, const SmallAcc& S, const KCtx& C,
                                       const int rel_now, int* acc_kn) {
     unsigned n_t1 = 0; int kn = 0;
     const int acc = parent_move<BigAcc, VERIFY>(P, child, d, L, C.big, S, C, rel_now, n_t1, kn);
@@ -507,7 +730,8 @@ __device__ __noinline__ Lane big_move(const SspsDev P, const int child, const St
 // The kernel
 // ------------------------------------------------------------------------------------------------
 template <class Source, bool VERIFY>
-__global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(SspsDev P, ChainState st, MhParams prm, Source src) {
+__global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(const __grid_constant__ SspsDev P, const __grid_constant__ ChainState st,
+                                                                              const __grid_constant__ MhParams prm, const __grid_constant__ Source src) {
     extern __shared__ double smem_d[];
     const int lane = threadIdx.x & 31;
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -579,7 +803,7 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(Ss
                 const int rel_now = ceil_div_i(l, thin) - 1;   // recorded samples of this launch that precede the change
                 int kn = 0;
                 if (L.mode == MODE_SMALL) {
-                    s_accp += (unsigned)parent_move<SmallAcc, VERIFY>(P, i, d, L, S, S, C, rel_now, s_t1, kn);
+                    s_accp += (unsigned)small_move<VERIFY>(P, i, d, L, S, C, rel_now, s_t1, kn);
                 } else {
                     int acc_kn = 0;
                     L = big_move<VERIFY>(P, i, d, L, S, C, rel_now, &acc_kn);
