@@ -118,7 +118,7 @@ struct ssps_handle {
     ChainState st{};
     int mh_grid = 0;
     size_t mh_smem = 0;
-    DevBuf<double> big_d, x_d;      // arenas: cached-inverse tier, exact scratch (per resident thread)
+    DevBuf<double> big_d, scr_d, x_d;   // BIG-tier factors (per resident thread), scratch factor (per resident warp), verify scratch
     DevBuf<uint32_t> big_w;
     DevBuf<uint16_t> big_r, x_t;
     DevBuf<int> task_counter, order;
@@ -488,12 +488,17 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     st.lam_sum = h->lam_sum.p; st.lam_sq = h->lam_sq.p;
 
     // persistent MH grid: as many CTAs as stay resident, never more than there are warp-tasks
-    h->mh_smem = (size_t)2 * SSPS_ROWLEN(SSPS_KS) * sizeof(double) * SSPS_BLOCK + (size_t)SSPS_KS * sizeof(uint32_t) * SSPS_BLOCK
+    h->mh_smem = (size_t)SSPS_ROWLEN(SSPS_KS) * sizeof(double) * SSPS_BLOCK + (size_t)SSPS_KS * sizeof(uint32_t) * SSPS_BLOCK
                + (size_t)SSPS_KS * SSPS_BLOCK;
     int occ = 1 << 30;
     {
+        // Shared memory holds only the SMALL-tier factors; what the carve-out leaves is L1 for the G / R / move
+        // tables.  First find the register-limited occupancy with the largest carve-out, then shrink the
+        // carve-out to what that many CTAs need (SSPS_CARVEOUT=<percent> overrides, for experiments).
         const void* fns[4] = {(const void*)mh_sweeps_kernel<PhiloxSource, false>, (const void*)mh_sweeps_kernel<PhiloxSource, true>,
                               (const void*)mh_sweeps_kernel<ReplaySource, false>, (const void*)mh_sweeps_kernel<ReplaySource, true>};
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, h->device));
         for (const void* f : fns) {
             int o = 0;
             CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
@@ -501,6 +506,11 @@ int alloc_chains(ssps_handle* h, int n_chains) {
             CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, f, SSPS_BLOCK, h->mh_smem));
             occ = std::min(occ, o);
         }
+        occ = std::max(1, occ);
+        int pct = (int)std::ceil(100.0 * (double)occ * (double)(h->mh_smem + 1024) / (double)prop.sharedMemPerMultiprocessor) + 2;
+        if (const char* e = getenv("SSPS_CARVEOUT")) pct = atoi(e);
+        pct = std::max(0, std::min(100, pct));
+        for (const void* f : fns) CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
     }
     occ = std::max(1, occ);
     const int n_tasks = V * (h->nch_pad / 32);
@@ -508,10 +518,11 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     h->mh_grid = std::max(1, std::min(h->sm_count * occ, div_up((size_t)n_tasks, warps_per_cta)));
     const size_t nthreads = (size_t)h->mh_grid * SSPS_BLOCK;
     const size_t kc = (size_t)h->kcap;
-    CK(h->big_d.alloc(nthreads * 2 * SSPS_ROWLEN(kc)));
+    CK(h->big_d.alloc(nthreads * SSPS_ROWLEN(kc)));
+    CK(h->scr_d.alloc(nthreads / 32 * SSPS_ROWLEN(kc)));
     CK(h->big_w.alloc(nthreads * kc));
     CK(h->big_r.alloc(nthreads * kc));
-    CK(h->x_d.alloc(nthreads * (SSPS_TRI(kc) + kc)));
+    CK(h->x_d.alloc(h->cfg.verify ? nthreads * (SSPS_TRI(kc) + kc) : 1));
     CK(h->x_t.alloc(nthreads * 2 * kc));
     CK(h->task_counter.alloc(1));
     CK(h->order.alloc(V)); CK(h->vcost.alloc(V));
@@ -703,7 +714,7 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
         prm.n_tasks = V * prm.n_slabs;
         prm.task_counter = h->task_counter.p;
         prm.order = h->order.p; prm.vcost = h->vcost.p;
-        prm.big_d = h->big_d.p; prm.big_w = h->big_w.p; prm.big_r = h->big_r.p;
+        prm.big_d = h->big_d.p; prm.big_w = h->big_w.p; prm.big_r = h->big_r.p; prm.scr_d = h->scr_d.p;
         prm.x_d = h->x_d.p; prm.x_t = h->x_t.p;
         prm.kcap = h->kcap; prm.stride = h->mh_grid * SSPS_BLOCK;
         prm.stats = h->stats.p;
@@ -1112,6 +1123,28 @@ int ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len) {
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaMemcpy(hh, h->khist.p, sizeof hh, cudaMemcpyDeviceToHost));
     for (int a = 0; a < len; ++a) hist[a] = a < 64 ? (int64_t)hh[a] : 0;
+    return SSPS_OK;
+}
+
+int ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles, int32_t* mean_indeg_x1000) {
+    CKS(bind(h));
+    if (h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "no chains");
+    const int V = h->V;
+    CK(cudaStreamSynchronize(h->stream));
+    if (cycles) {
+        std::vector<unsigned long long> c(V);
+        CK(cudaMemcpy(c.data(), h->vcost.p, sizeof(unsigned long long) * V, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < V; ++i) cycles[i] = (int64_t)c[i];
+    }
+    if (mean_indeg_x1000) {
+        std::vector<int> k((size_t)V * h->nch_pad);
+        CK(cudaMemcpy(k.data(), h->k.p, sizeof(int) * k.size(), cudaMemcpyDeviceToHost));
+        for (int i = 0; i < V; ++i) {
+            long long s = 0;
+            for (int c = 0; c < h->n_chains; ++c) s += k[(size_t)i * h->nch_pad + c];
+            mean_indeg_x1000[i] = (int32_t)(1000 * s / h->n_chains);
+        }
+    }
     return SSPS_OK;
 }
 

@@ -31,8 +31,8 @@
 // with fp32 MUFU logarithms and compared with a margin that bounds the screening error; if they
 // are closer than the margin the test is redone in the reference order with fp64 logarithms.
 //
-// Storage tiers for (ids, factor, scratch) of a lane: |S| <= SSPS_KS in shared memory, larger
-// sets in a coalesced global arena (L1/L2-resident, touched only by the few lanes that need it).
+// Storage tiers for (ids, factor) of a lane: |S| <= SSPS_KS in shared memory, each lane on its own;
+// larger sets in a global arena, processed by the WHOLE WARP one lane at a time (see "Tier storage").
 #pragma once
 #include "ssps_kernels.cuh"
 
@@ -47,7 +47,7 @@
 #endif
 #define SSPS_LN2 0.6931471805599453
 
-enum { MODE_SMALL = 0, MODE_BIG = 1 };
+enum { MODE_SMALL = 0, MODE_BIG = 1, MODE_PROMOTE = 2 };
 // stats slots (unsigned long long each)
 enum { ST_ACCP = 0, ST_ACCL = 1, ST_SUMK = 2, ST_F3 = 3, ST_BYTES = 4, ST_OVERFLOW = 5, ST_PROP = 6, ST_TIER1 = 7,
        ST_MISMATCH = 10, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_N = 16 };
@@ -128,49 +128,45 @@ __global__ void export_draws_kernel(PhiloxSource src, int n_chains, int V, int64
 }
 
 // ------------------------------------------------------------------------------------------------
-// Tier storage.  Slot a (arrival order) holds: word = id | rel << 16 (`rel` = recorded samples of
-// this launch that precede the parent's arrival: lazy tally), rank = position of the id in the
-// SORTED parent list (the reference's moves are defined on the sorted list,
-// dbn_proposals.jl:19-49), row a of the factor: Lo(a, b) for b < a, Li(a) = 1/d_a, Wv(a) = w_a.
-// The scratch factor So/Si/Sw is indexed by the PROPOSED set's arrival positions.
+// Tier storage.  Slot a (arrival order) of a micro-chain holds: word = id | rel << 16 (`rel` =
+// recorded samples of this launch that precede the parent's arrival: lazy tally), rank = position
+// of the id in the SORTED parent list (the reference's moves are defined on the sorted list,
+// dbn_proposals.jl:19-49), and row a of the factor: L(a, b) for b < a, 1/d_a, w_a.
+//
+//   SMALL  |S| <= SSPS_KS : shared memory, element-major [e][thread]; every lane works on its own
+//          micro-chain, statically unrolled (small_move).
+//   BIG    |S| >  SSPS_KS : a global arena, one contiguous block per lane; the WHOLE WARP works on
+//          one such lane at a time (coop_eval / coop_commit) while the others wait -- big sets are
+//          rare (< 1 % of the proposals at the metric point) but cost O(k^2)..O(k^3), so one lane
+//          grinding through them alone would hold its 31 neighbours for the whole step.
 // ------------------------------------------------------------------------------------------------
-#define SSPS_ROWLEN(K) (SSPS_TRI(K) + (K))          // off-diagonals + diagonal, then w: TRI(K) + K doubles
+#define SSPS_ROWLEN(K) (SSPS_TRI(K) + (K))          // rows incl. the 1/d slots: TRI(K) doubles, then w: K doubles
+#define SSPS_FULL 0xffffffffu
+#define SSPS_KU 4                                    // a lane owns columns lane + 32 u, u < SSPS_KU: kcap <= 128
 
 struct SmallAcc {   // shared memory, element-major: [e][thread]
     double* d; uint32_t* w; uint8_t* r;
-    static constexpr bool is_small = true;
-    __device__ __forceinline__ int cap() const { return SSPS_KS; }
-    __device__ __forceinline__ double& D(int e) const { return d[e * SSPS_BLOCK]; }
     __device__ __forceinline__ double& Lo(int a, int b) const { return d[(SSPS_TRI(a) + b) * SSPS_BLOCK]; }
     __device__ __forceinline__ double& Li(int a) const { return d[(SSPS_TRI(a) + a) * SSPS_BLOCK]; }
     __device__ __forceinline__ double& Wv(int a) const { return d[(SSPS_TRI(SSPS_KS) + a) * SSPS_BLOCK]; }
-    __device__ __forceinline__ double& So(int a, int b) const { return d[(SSPS_ROWLEN(SSPS_KS) + SSPS_TRI(a) + b) * SSPS_BLOCK]; }
-    __device__ __forceinline__ double& Si(int a) const { return d[(SSPS_ROWLEN(SSPS_KS) + SSPS_TRI(a) + a) * SSPS_BLOCK]; }
-    __device__ __forceinline__ double& Sw(int a) const { return d[(SSPS_ROWLEN(SSPS_KS) + SSPS_TRI(SSPS_KS) + a) * SSPS_BLOCK]; }
     __device__ __forceinline__ uint32_t& W(int a) const { return w[a * SSPS_BLOCK]; }
     __device__ __forceinline__ int rank(int a) const { return (int)r[a * SSPS_BLOCK]; }
     __device__ __forceinline__ void set_rank(int a, int v) const { r[a * SSPS_BLOCK] = (uint8_t)v; }
+    __device__ __forceinline__ SmallAcc of_lane(int delta) const { SmallAcc o; o.d = d + delta; o.w = w + delta; o.r = r + delta; return o; }
 };
-struct BigAcc {     // global arena, element-major over all resident threads: [e][gtid]
-    double* d; uint32_t* w; uint16_t* r; int stride, kcap;
-    static constexpr bool is_small = false;
-    __device__ __forceinline__ int cap() const { return kcap; }
-    __device__ __forceinline__ double& D(int e) const { return d[(unsigned)e * (unsigned)stride]; }
-    __device__ __forceinline__ double& Lo(int a, int b) const { return d[(unsigned)(SSPS_TRI(a) + b) * (unsigned)stride]; }
-    __device__ __forceinline__ double& Li(int a) const { return d[(unsigned)(SSPS_TRI(a) + a) * (unsigned)stride]; }
-    __device__ __forceinline__ double& Wv(int a) const { return d[(unsigned)(SSPS_TRI(kcap) + a) * (unsigned)stride]; }
-    __device__ __forceinline__ double& So(int a, int b) const { return d[(unsigned)(SSPS_ROWLEN(kcap) + SSPS_TRI(a) + b) * (unsigned)stride]; }
-    __device__ __forceinline__ double& Si(int a) const { return d[(unsigned)(SSPS_ROWLEN(kcap) + SSPS_TRI(a) + a) * (unsigned)stride]; }
-    __device__ __forceinline__ double& Sw(int a) const { return d[(unsigned)(SSPS_ROWLEN(kcap) + SSPS_TRI(kcap) + a) * (unsigned)stride]; }
-    __device__ __forceinline__ uint32_t& W(int a) const { return w[(unsigned)a * (unsigned)stride]; }
-    __device__ __forceinline__ int rank(int a) const { return (int)r[(unsigned)a * (unsigned)stride]; }
-    __device__ __forceinline__ void set_rank(int a, int v) const { r[(unsigned)a * (unsigned)stride] = (uint16_t)v; }
+
+// one lane's block of the BIG arena + the warp's scratch factor (same shape, proposed set's coordinates)
+struct BigRef {
+    double* f; double* s; uint32_t* w; uint16_t* r; int kcap;
+    __device__ __forceinline__ double* fw() const { return f + SSPS_TRI(kcap); }
+    __device__ __forceinline__ double* sw() const { return s + SSPS_TRI(kcap); }
+    __device__ __forceinline__ int id(int a) const { return (int)(w[a] & 0xffffu); }
 };
 
 struct Lane {
     double lam, somc, q, ip, nrmf;   // nrmf: screening value of the prior normaliser at lam
     float lg_ip;                     // lg2(ip), screening
-    int k, mode, n_pev;
+    int k, mode, n_pev, pend_j;      // pend_j: the parent whose accepted arrival outgrew the SMALL tier
 };
 
 struct MhParams {
@@ -181,9 +177,9 @@ struct MhParams {
     int* task_counter;
     const int* order;        // vertices, most expensive first
     unsigned long long* vcost;   // per-vertex cycles of this launch
-    // global arenas, per resident thread
-    double* big_d; uint32_t* big_w; uint16_t* big_r;      // factor + scratch of lanes with |S| > SSPS_KS
-    double* x_d; uint16_t* x_t;                            // from-scratch scorer scratch: L, w | T, S
+    // BIG tier: per resident thread [gtid][ROWLEN(kcap)] / [gtid][kcap]; scratch factor per resident warp
+    double* big_d; uint32_t* big_w; uint16_t* big_r; double* scr_d;
+    double* x_d; uint16_t* x_t;                            // per-thread id lists (x_t) and from-scratch scorer scratch (x_d: verify only)
     int kcap; int stride;
     unsigned long long* stats;
     unsigned long long* khist;   // nullable, 64 bins
@@ -193,11 +189,19 @@ struct MhParams {
 };
 
 struct KCtx {       // per-lane pointers
-    BigAcc big; Scratch xs;
+    double* big_d0; uint32_t* big_w0; uint16_t* big_r0;    // arena block of lane 0 of this warp
+    double* scr;                                           // this warp's scratch factor
+    Scratch xs;
     uint32_t* cnt_row;     // counts + mc * V
     uint32_t* pev;         // pev + mc * pev_cap (nullable)
     int pev_cap, kcap;
     unsigned long long* stats;
+    __device__ __forceinline__ BigRef big(int ln) const {
+        BigRef b;
+        b.f = big_d0 + (size_t)ln * SSPS_ROWLEN(kcap); b.s = scr;
+        b.w = big_w0 + (size_t)ln * kcap; b.r = big_r0 + (size_t)ln * kcap; b.kcap = kcap;
+        return b;
+    }
 };
 
 __device__ __forceinline__ int ceil_div_i(int a, int b) { return (a + b - 1) / b; }
@@ -214,6 +218,22 @@ __device__ __forceinline__ double normaliser_fast(const SspsDev& P, int child, d
     return acc;
 }
 
+// the SORTED current set of this lane -> xs.S(0..k-1)
+__device__ __noinline__ void write_sorted(const int mode, const SmallAcc& S, const BigRef& B, const Scratch& xs, const int k) {
+    if (mode == MODE_BIG) { for (int b = 0; b < k; ++b) xs.S((int)B.r[b]) = (uint16_t)B.id(b); }
+    else { for (int b = 0; b < k; ++b) xs.S(S.rank(b)) = (uint16_t)(S.W(b) & 0xffffu); }
+}
+
+// sum of (1 - c) over the current set, in the reference's (sorted) order
+__device__ __noinline__ double sorted_somc(const SspsDev& P, const int child, const int mode, const SmallAcc& S, const BigRef& B,
+                                           const Scratch& xs, const int k) {
+    write_sorted(mode, S, B, xs, k);
+    const double* __restrict__ omc_i = P.omc + (size_t)P.V * child;
+    double somc = 0.0;
+    for (int a = 0; a < k; ++a) somc += __ldg(omc_i + xs.S(a));
+    return somc;
+}
+
 // lambda move in the reference order (the oracle's chain_step restates exactly this); xs.S(0..k-1)
 // holds the SORTED current set
 __device__ __noinline__ int lambda_exact_decide(const SspsDev& P, const int child, const Scratch& xs, const int k, const double lam,
@@ -226,218 +246,34 @@ __device__ __noinline__ int lambda_exact_decide(const SspsDev& P, const int chil
     return log(u_lam) < w ? 1 : 0;
 }
 
-__device__ __noinline__ void write_sorted(const int mode, const SmallAcc& S, const BigAcc& B, const Scratch& xs, const int k) {
-    if (mode == MODE_SMALL) { for (int b = 0; b < k; ++b) xs.S(S.rank(b)) = (uint16_t)(S.W(b) & 0xffffu); }
-    else { for (int b = 0; b < k; ++b) xs.S(B.rank(b)) = (uint16_t)(B.W(b) & 0xffffu); }
-}
-
 // ------------------------------------------------------------------------------------------------
-// One row of the arrival-order Cholesky, written to the scratch factor at (new) position a.
-//   p      arrival position being removed (p >= k: none); rows < p of the cached factor are reused
-//   b0     entries b < b0 of this row are taken from cached row `old_row` (unchanged by the removal)
-// Operation order = orc_lml_chol / score_set: l_b = (G - sum_{m<b} l_m L_bm) / d_b,
-// d2 = G_jj - sum l_m^2, t = r_j - sum l_m w_m, each sum in ascending m with fma.
+// Pieces shared by both tiers
 // ------------------------------------------------------------------------------------------------
-// Where a freshly computed row lives in the scratch factor: element offsets of its off-diagonals, 1/d and w.
-struct RowAt { int lo, inv, w; };
-template <class A>
-__device__ __forceinline__ RowAt scratch_row(const A& F, int a) {       // row a of the scratch factor
-    const int K = F.cap();
-    RowAt r; r.lo = SSPS_ROWLEN(K) + SSPS_TRI(a); r.inv = r.lo + a; r.w = SSPS_ROWLEN(K) + SSPS_TRI(K) + a;
-    return r;
-}
-template <class A>
-__device__ __forceinline__ RowAt scratch_flat(const A& F) {             // a lone appended row (pure add): start of the scratch
-    const int K = F.cap();
-    RowAt r; r.lo = SSPS_ROWLEN(K); r.inv = r.lo + K; r.w = r.inv + 1;
-    return r;
+// one Cholesky pivot (orc_lml_chol / score_set): accepted -> (1/d, t/d), q += w^2; numerically
+// dependent column -> contributes nothing; NaN data (zero-variance column, quirk Q4) -> NaN
+__device__ __forceinline__ void chol_pivot(const double d2, const double gjj, const double t, double& inv, double& w, double& q) {
+    if (d2 > SSPS_PIVOT_TOL * gjj) { inv = 1.0 / sqrt(d2); w = t * inv; q = fma(w, w, q); }
+    else if (d2 != d2 || gjj != gjj) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; q = inv; }
+    else { inv = 0.0; w = 0.0; }
 }
 
-template <class A>
-__device__ __forceinline__ double factor_row(const SspsDev& P, const double* __restrict__ Ri, const A& F, const int p, const int a,
-                                             const int ja, const int b0, const int old_row, const RowAt at, double q) {
-    const double* __restrict__ Gj = P.G + (size_t)ja * P.V;
-    const double gjj = __ldg(Gj + ja);
-    double d2 = gjj, t = __ldg(Ri + ja);
-    for (int b = 0; b < a; ++b) {
-        double l;
-        if (b < b0) l = F.Lo(old_row, b);
-        else {
-            const int jb = (int)(F.W(b >= p ? b + 1 : b) & 0xffffu);
-            double s = __ldg(Gj + jb);
-            if (b < p) {                         // row b of the cached factor
-                for (int m = 0; m < b; ++m) s = fma(-((m < b0) ? F.Lo(old_row, m) : F.D(at.lo + m)), F.Lo(b, m), s);
-                l = s * F.Li(b);
-            } else {                             // row b was recomputed: entries < p from cached row b+1, the rest from scratch
-                for (int m = 0; m < b; ++m)
-                    s = fma(-((m < b0) ? F.Lo(old_row, m) : F.D(at.lo + m)), (m < p) ? F.Lo(b + 1, m) : F.So(b, m), s);
-                l = s * F.Si(b);
-            }
-            F.D(at.lo + b) = l;
-        }
-        d2 = fma(-l, l, d2);
-        t = fma(-l, (b < p) ? F.Wv(b) : F.Sw(b), t);
-    }
-    if (d2 > SSPS_PIVOT_TOL * gjj) {
-        const double invd = 1.0 / sqrt(d2);
-        const double wa = t * invd;
-        F.D(at.inv) = invd; F.D(at.w) = wa;
-        q = fma(wa, wa, q);
-    } else if (d2 != d2 || gjj != gjj) {           // NaN data: zero-variance column (quirk Q4)
-        const double nan = __longlong_as_double(0x7ff8000000000000LL);
-        F.D(at.inv) = nan; F.D(at.w) = nan; q = nan;
-    } else {                                       // numerically dependent column: contributes nothing
-        F.D(at.inv) = 0.0; F.D(at.w) = 0.0;
-    }
-    return q;
-}
-
-// q of the proposed set (remove arrival position p if p < k, then append j_add if >= 0); the new
-// rows p .. kn-1 are left in the scratch factor
-template <class A>
-__device__ __forceinline__ double eval_move(const SspsDev& P, const double* __restrict__ Ri, const A& F, const int k, const int p,
-                                            const int j_add) {
-    double q = 0.0;
-    const int pm = p < k ? p : k;
-    for (int m = 0; m < pm; ++m) { const double wm = F.Wv(m); q = fma(wm, wm, q); }
-    const int kr = p < k ? k - 1 : k;
-    for (int a = p; a < kr; ++a) q = factor_row(P, Ri, F, p, a, (int)(F.W(a + 1) & 0xffffu), p, a + 1, scratch_row(F, a), q);
-    if (j_add >= 0) q = factor_row(P, Ri, F, p, kr, j_add, 0, 0, p < k ? scratch_row(F, kr) : scratch_flat(F), q);
-    return q;
-}
-
-// accepted: fold the scratch rows into the cached factor, edit the id list (tallies, change points, ranks)
-template <class A>
-__device__ __forceinline__ void commit_move(const A& F, const KCtx& C, Lane& L, const int p, const int j_add, const int j_rem,
-                                            const int rel_now) {
-    int k = L.k;
-    if (p < k) {
-        const uint32_t slw = F.W(p);
-        const int credit = rel_now - (int)(slw >> 16);
-        if (credit > 0) C.cnt_row[j_rem] += (uint32_t)credit;
-        if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
-        const int rp = F.rank(p);
-        for (int a = 0; a < k; ++a) { const int ra = F.rank(a); if (ra > rp) F.set_rank(a, ra - 1); }
-        for (int a = p; a < k - 1; ++a) {
-            for (int m = 0; m < p; ++m) F.Lo(a, m) = F.Lo(a + 1, m);
-            for (int m = p; m < a; ++m) F.Lo(a, m) = F.So(a, m);
-            F.Li(a) = F.Si(a); F.Wv(a) = F.Sw(a);
-            F.W(a) = F.W(a + 1); F.set_rank(a, F.rank(a + 1));
-        }
-        --k;
-    }
-    if (j_add >= 0) {
-        const RowAt at = p < L.k ? scratch_row(F, k) : scratch_flat(F);     // k is already the post-removal size
-        for (int m = 0; m < k; ++m) F.Lo(k, m) = F.D(at.lo + m);
-        F.Li(k) = F.D(at.inv); F.Wv(k) = F.D(at.w);
-        int rj = 0;
-        for (int a = 0; a < k; ++a) {
-            if ((int)(F.W(a) & 0xffffu) < j_add) ++rj; else F.set_rank(a, F.rank(a) + 1);
-        }
-        F.W(k) = (uint32_t)j_add | ((uint32_t)rel_now << 16);
-        F.set_rank(k, rj);
-        if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
-        ++k;
-    }
-    L.k = k;
-}
-
-__device__ __forceinline__ void lane_set_q(const SspsDev& P, int child, Lane& L, double q) {
-    L.q = q; L.ip = __ldg(P.yty + child) - P.shrink * q; L.lg_ip = fast_lg2((float)L.ip);
-}
-
-// factor of the current set from its id list (task start, tier changes): the same rows, in order
-template <class A>
-__device__ __forceinline__ double build_factor(const SspsDev& P, const double* __restrict__ Ri, const A& F, const int k) {
-    double q = 0.0;
-    for (int a = 0; a < k; ++a) {
-        // p = a: "rows < a cached, nothing removed yet" -- factor_row reads rows < a from the cached factor and writes row a
-        // to scratch; fold it in at once
-        const RowAt at = scratch_flat(F);
-        q = factor_row(P, Ri, F, k, a, (int)(F.W(a) & 0xffffu), 0, 0, at, q);
-        for (int m = 0; m < a; ++m) F.Lo(a, m) = F.D(at.lo + m);
-        F.Li(a) = F.D(at.inv); F.Wv(a) = F.D(at.w);
-    }
-    return q;
-}
-
-// ids (word, rank) of the lane are in the arena; build its factor in the tier its size selects
-__device__ __noinline__ Lane lane_settle(const SspsDev& P, const int child, Lane L, const SmallAcc& S, const KCtx& C) {
-    const int k = L.k;
-    const double* __restrict__ omc_i = P.omc + (size_t)P.V * child;
-    const double* __restrict__ Ri = P.R + (size_t)P.V * child;
-    for (int b = 0; b < k; ++b) C.xs.S(C.big.rank(b)) = (uint16_t)(C.big.W(b) & 0xffffu);
-    double somc = 0.0;
-    for (int a = 0; a < k; ++a) somc += __ldg(omc_i + C.xs.S(a));      // the reference-order (sorted) sum
-    L.somc = somc;
-    if (k <= SSPS_KS) {
-        for (int b = 0; b < k; ++b) { S.W(b) = C.big.W(b); S.set_rank(b, C.big.rank(b)); }
-        L.mode = MODE_SMALL;
-        lane_set_q(P, child, L, build_factor<SmallAcc>(P, Ri, S, k));
-    } else {
-        L.mode = MODE_BIG;
-        lane_set_q(P, child, L, build_factor<BigAcc>(P, Ri, C.big, k));
-    }
-    return L;
-}
-
-// a SMALL lane accepted a move that outgrows shared memory: hand ids over to the arena, rebuild there
-__device__ __noinline__ Lane small_to_big(const SspsDev& P, const int child, Lane L, const SmallAcc& S, const KCtx& C, const int p,
-                                          const int j_add, const int j_rem, const int rel_now) {
-    const int k = L.k;
-    for (int b = 0; b < k; ++b) { C.big.W(b) = S.W(b); C.big.set_rank(b, S.rank(b)); }
-    // edit the id list only (the factor is rebuilt): reuse commit_move's bookkeeping on a dummy factor region
-    if (p < k) {
-        const uint32_t slw = C.big.W(p);
-        const int credit = rel_now - (int)(slw >> 16);
-        if (credit > 0) C.cnt_row[j_rem] += (uint32_t)credit;
-        if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
-        const int rp = C.big.rank(p);
-        for (int a = 0; a < k; ++a) { const int ra = C.big.rank(a); if (ra > rp) C.big.set_rank(a, ra - 1); }
-        for (int a = p; a < k - 1; ++a) { C.big.W(a) = C.big.W(a + 1); C.big.set_rank(a, C.big.rank(a + 1)); }
-        L.k = k - 1;
-    }
-    if (j_add >= 0) {
-        const int kk = L.k;
-        int rj = 0;
-        for (int a = 0; a < kk; ++a) {
-            if ((int)(C.big.W(a) & 0xffffu) < j_add) ++rj; else C.big.set_rank(a, C.big.rank(a) + 1);
-        }
-        C.big.W(kk) = (uint32_t)j_add | ((uint32_t)rel_now << 16);
-        C.big.set_rank(kk, rj);
-        if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
-        L.k = kk + 1;
-    }
-    return lane_settle(P, child, L, S, C);
-}
-
-// ------------------------------------------------------------------------------------------------
-// The parent-set move (smart_proposal + smart_involution + Gen.mh), generic over the tier.
-// Returns 1 if accepted.  kn_out = |S'|.
-// ------------------------------------------------------------------------------------------------
-template <class A, bool VERIFY>
-__device__ __forceinline__ int parent_move(const SspsDev& P, const int child, const StepDraws& d, Lane& L, const A& F, const SmallAcc& S,
-                                           const KCtx& C, const int rel_now, unsigned& n_t1, int& kn_out) {
-    const int V = P.V, k = L.k;
+// smart_proposal (dbn_proposals.jl:60-80): the action and the two ordinal draws (1-based; 0 = not drawn)
+__device__ __forceinline__ void select_move(const SspsDev& P, const int child, const int k, const StepDraws& d, int& action, int& a_ord,
+                                            int& r_ord) {
+    const int V = P.V;
     const size_t trow = ((size_t)child * (V + 1) + k) * 3;
     const double p_add = __ldg(P.mvP + trow), p_swp = __ldg(P.mvP + trow + 1);
-    const int action = d.u_act < p_add ? ACT_ADD : (d.u_act < p_add + p_swp ? ACT_SWAP : ACT_REM);
-    const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
-    int j_add = -1, j_rem = -1, p = k;
-    if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
-        const int m = V - k;
-        int a = 1 + (int)floor(d.u_add * (double)m); if (a > m) a = m;
-        int c = 0;
-        for (int b = 0; b < k; ++b) c += ((int)(F.W(b) & 0xffffu) - F.rank(b) < a) ? 1 : 0;
-        j_add = a - 1 + c;
-    }
-    if (has_rem) {          // the r-th element of the sorted list
-        int r = 1 + (int)floor(d.u_rem * (double)k); if (r > k) r = k;
-        for (int b = 0; b < k; ++b) if (F.rank(b) == r - 1) { p = b; j_rem = (int)(F.W(b) & 0xffffu); }
-    }
-    const int kn = k + (has_add ? 1 : 0) - (has_rem ? 1 : 0);
-    kn_out = kn;
-    double fwd = 0.0, bwd = 0.0;
+    action = d.u_act < p_add ? ACT_ADD : (d.u_act < p_add + p_swp ? ACT_SWAP : ACT_REM);
+    a_ord = 0; r_ord = 0;
+    if (action != ACT_REM) { const int m = V - k; int a = 1 + (int)floor(d.u_add * (double)m); if (a > m) a = m; a_ord = a; }
+    if (action != ACT_ADD) { int r = 1 + (int)floor(d.u_rem * (double)k); if (r > k) r = k; r_ord = r; }
+}
+
+// log proposal probabilities of the move and of its reverse (smart_involution, dbn_proposals.jl:83-130); swaps cancel
+__device__ __forceinline__ void move_ratio(const SspsDev& P, const int child, const int k, const int action, double& fwd, double& bwd) {
+    const int V = P.V;
+    const size_t trow = ((size_t)child * (V + 1) + k) * 3;
+    fwd = 0.0; bwd = 0.0;
     if (action == ACT_ADD) {
         fwd = __ldg(P.mvLogP + trow) - __ldg(P.logint + (V - k));
         bwd = __ldg(P.mvLogP + ((size_t)child * (V + 1) + (k + 1)) * 3 + 2) - __ldg(P.logint + (k + 1));
@@ -445,70 +281,82 @@ __device__ __forceinline__ int parent_move(const SspsDev& P, const int child, co
         fwd = __ldg(P.mvLogP + trow + 2) - __ldg(P.logint + k);
         bwd = __ldg(P.mvLogP + ((size_t)child * (V + 1) + (k - 1)) * 3 + 0) - __ldg(P.logint + (V - k + 1));
     }
-    if (kn > C.kcap) { atomicExch(C.stats + ST_OVERFLOW, 1ull); return 0; }
-    const double* __restrict__ omc_i = P.omc + (size_t)V * child;
-    double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
-    if (has_add) { omc_add = __ldg(omc_i + j_add); dprior = -L.lam * omc_add; }
-    if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
+}
 
-    const double q_new = eval_move(P, P.R + (size_t)V * child, F, k, p, j_add);
-    const double ip_new = __ldg(P.yty + child) - P.shrink * q_new;
-
-    // ---- screened acceptance test: accept iff log(u) < alpha ----
-    const float lgu = fast_lg2((float)d.u_acc);
-    const float lg_new = fast_lg2((float)ip_new);
+// Gen.mh: accept iff log(u) < alpha.  Both sides are first formed with fp32 MUFU logarithms and compared
+// with a margin that bounds the screening error; closer than the margin -> the reference-order fp64 test.
+__device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
+                                          const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
+                                          const double ip_new, const float lg_new, const double u_acc, unsigned& n_t1) {
+    const float lgu = fast_lg2((float)u_acc);
     const double hn = 0.5 * P.dn;
     const double base = ((dprior - fwd) + bwd) - 0.5 * (double)(kn - k) * P.log1pn;
-    const double diff = SSPS_LN2 * ((double)lgu + hn * ((double)lg_new - (double)L.lg_ip)) - base;
-    const double marg = 1.2e-6 * ((double)fabsf(lgu) + 1.0 + hn * ((double)(fabsf(lg_new) + fabsf(L.lg_ip)) + 2.0)) + 1e-9 * fabs(base) + 1e-6;
+    const double diff = SSPS_LN2 * ((double)lgu + hn * ((double)lg_new - (double)lg_ip_cur)) - base;
+    const double marg = 1.2e-6 * ((double)fabsf(lgu) + 1.0 + hn * ((double)(fabsf(lg_new) + fabsf(lg_ip_cur)) + 2.0)) + 1e-9 * fabs(base) + 1e-6;
     bool accept = diff < 0.0;
-    if (!(d.u_acc > 1e-30 && fabs(diff) > marg)) {        // too close (or NaN): the reference-order fp64 test
+    if (!(u_acc > 1e-30 && fabs(diff) > marg)) {        // too close (or NaN): the reference-order fp64 test
         ++n_t1;
-        const double lml_cur = -0.5 * (double)k * P.log1pn - 0.5 * P.dn * log(L.ip);
+        const double lml_cur = -0.5 * (double)k * P.log1pn - 0.5 * P.dn * log(ip_cur);
         const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
         const double w = dprior + (lml_new - lml_cur);
         const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
-        accept = log(d.u_acc) < alpha;
+        accept = log(u_acc) < alpha;
     }
-    if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
-        int t = 0;
-        for (int b = 0; b < k; ++b) if (b != p) C.xs.T(t++) = (uint16_t)(F.W(b) & 0xffffu);
-        if (j_add >= 0) C.xs.T(t++) = (uint16_t)j_add;
-        const double lml_ref = score_set(P, child, C.xs, t, nullptr);
-        const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
-        if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
-    }
-    if (!accept) return 0;
+    return accept;
+}
 
-    if (A::is_small && kn > SSPS_KS) {     // SMALL lane outgrows shared memory
-        L = small_to_big(P, child, L, S, C, p, j_add, j_rem, rel_now);
-        return 1;
-    }
-    commit_move(F, C, L, p, j_add, j_rem, rel_now);
-    L.somc = (L.somc - omc_rem) + omc_add;
-    L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
-    return 1;
+__device__ __forceinline__ void lane_set_q(const SspsDev& P, int child, Lane& L, double q) {
+    L.q = q; L.ip = __ldg(P.yty + child) - P.shrink * q; L.lg_ip = fast_lg2((float)L.ip);
 }
 
 // ------------------------------------------------------------------------------------------------
-// The parent-set move of a SMALL lane (|S| <= SSPS_KS): same arithmetic as parent_move<SmallAcc>,
-// but statically unrolled over SSPS_KS slots with the proposed set's factor held in REGISTERS, so
-// that the 32 lanes of a warp (different k, different removal position p) walk one instruction
-// stream: rows/entries a lane does not need are predicated off, rows nobody needs are skipped by a
-// warp-uniform branch.  NL(a, b) = entry (a, b) of the factor in the PROPOSED set's coordinates
-// (arrival positions after the removal): rows < p and the entries < p of later rows are the
-// cached values, the rest is recomputed; the appended parent's row is jl[].
+// SMALL tier: factor of the current set from its id list (task start, arrivals from the BIG tier).
+// Operation order = orc_lml_chol: l_b = (G_ab - sum_{m<b} l_m L_bm) / d_b, d2 = G_aa - sum l_m^2,
+// t = r_a - sum l_m w_m, each sum in ascending m with fma.
+// ------------------------------------------------------------------------------------------------
+__device__ __noinline__ double small_build(const SspsDev& P, const double* __restrict__ Ri, const SmallAcc& S, const int k) {
+    double q = 0.0;
+    for (int a = 0; a < k; ++a) {
+        const int ja = (int)(S.W(a) & 0xffffu);
+        const double* __restrict__ Ga = P.G + (size_t)ja * P.V;
+        const double gaa = __ldg(Ga + ja);
+        double d2 = gaa, t = __ldg(Ri + ja);
+        for (int b = 0; b < a; ++b) {
+            double s = __ldg(Ga + (int)(S.W(b) & 0xffffu));
+            for (int m = 0; m < b; ++m) s = fma(-S.Lo(a, m), S.Lo(b, m), s);
+            const double l = s * S.Li(b);
+            S.Lo(a, b) = l;
+            d2 = fma(-l, l, d2);
+            t = fma(-l, S.Wv(b), t);
+        }
+        double inv, w;
+        chol_pivot(d2, gaa, t, inv, w, q);
+        S.Li(a) = inv; S.Wv(a) = w;
+    }
+    return q;
+}
+
+// ------------------------------------------------------------------------------------------------
+// The parent-set move of a SMALL lane (|S| <= SSPS_KS), statically unrolled over SSPS_KS slots with
+// the proposed set's factor held in REGISTERS, so that the lanes of a warp (different k, different
+// removal position p) walk one instruction stream: rows/entries a lane does not need are
+// predicated off, rows nobody needs are skipped by a warp-uniform branch.  NL(a, b) = entry (a, b)
+// of the factor in the PROPOSED set's coordinates (arrival positions after the removal): rows < p
+// and the entries < p of later rows are the cached values, the rest is recomputed -- exactly the
+// rows a from-scratch factorisation of the proposed set (in its arrival order) would compute; the
+// appended parent's row is jl[].
+// An accepted arrival that outgrows the tier leaves the lane in MODE_PROMOTE (ids and factor still
+// those of the current set, L.pend_j = the arriving parent); the warp finishes it in big_phase.
 // ------------------------------------------------------------------------------------------------
 #define NL(a, b) nl[SSPS_TRI(a) - (a) + (b)]       // strictly lower triangle: row a starts at a(a-1)/2
 
 template <bool VERIFY>
 __device__ __forceinline__ int small_move(const SspsDev& P, const int child, const StepDraws& d, Lane& L, const SmallAcc& S,
-                                          const KCtx& C, const int rel_now, unsigned& n_t1, int& kn_out) {
+                                          const KCtx& C, const int rel_now, const unsigned peers, unsigned& n_t1, int& kn_out) {
     constexpr int KS = SSPS_KS;
     const int V = P.V, k = L.k;
-    const size_t trow = ((size_t)child * (V + 1) + k) * 3;
-    const double p_add = __ldg(P.mvP + trow), p_swp = __ldg(P.mvP + trow + 1);
-    const int action = d.u_act < p_add ? ACT_ADD : (d.u_act < p_add + p_swp ? ACT_SWAP : ACT_REM);
+    int action, a_ord, r_ord;
+    select_move(P, child, k, d, action, a_ord, r_ord);
     const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
 
     uint32_t idw[KS]; int rk[KS];
@@ -519,31 +367,21 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     }
     int j_add = -1, j_rem = -1, p = k, rp = 1 << 20;
     if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
-        const int m = V - k;
-        int a = 1 + (int)floor(d.u_add * (double)m); if (a > m) a = m;
         int c = 0;
 #pragma unroll
-        for (int b = 0; b < KS; ++b) c += (b < k && (int)(idw[b] & 0xffffu) - rk[b] < a) ? 1 : 0;
-        j_add = a - 1 + c;
+        for (int b = 0; b < KS; ++b) c += (b < k && (int)(idw[b] & 0xffffu) - rk[b] < a_ord) ? 1 : 0;
+        j_add = a_ord - 1 + c;
     }
     if (has_rem) {          // the r-th element of the sorted list
-        int r = 1 + (int)floor(d.u_rem * (double)k); if (r > k) r = k;
-        rp = r - 1;
+        rp = r_ord - 1;
 #pragma unroll
         for (int b = 0; b < KS; ++b) if (rk[b] == rp) { p = b; j_rem = (int)(idw[b] & 0xffffu); }
     }
     const int kr = k - (has_rem ? 1 : 0);
     const int kn = kr + (has_add ? 1 : 0);
     kn_out = kn;
-    double fwd = 0.0, bwd = 0.0;
-    if (action == ACT_ADD) {
-        fwd = __ldg(P.mvLogP + trow) - __ldg(P.logint + (V - k));
-        bwd = __ldg(P.mvLogP + ((size_t)child * (V + 1) + (k + 1)) * 3 + 2) - __ldg(P.logint + (k + 1));
-    } else if (action == ACT_REM) {
-        fwd = __ldg(P.mvLogP + trow + 2) - __ldg(P.logint + k);
-        bwd = __ldg(P.mvLogP + ((size_t)child * (V + 1) + (k - 1)) * 3 + 0) - __ldg(P.logint + (V - k + 1));
-    }
-    if (kn > C.kcap) { atomicExch(C.stats + ST_OVERFLOW, 1ull); return 0; }
+    double fwd, bwd;
+    move_ratio(P, child, k, action, fwd, bwd);
     const double* __restrict__ omc_i = P.omc + (size_t)V * child;
     const double* __restrict__ Ri = P.R + (size_t)V * child;
     double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
@@ -562,8 +400,9 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
 
     // the cached factor in the reduced set's coordinates; entries to recompute start as 0
     double nl[SSPS_TRI(KS) - KS + 1], ninv[KS], nw[KS];
-    const int kr_max = __reduce_max_sync(__activemask(), kr);
-    const int p_min = __reduce_min_sync(__activemask(), p);
+    const int kr_max = __reduce_max_sync(peers, kr);
+    const int p_min = __reduce_min_sync(peers, p);
+    if (kn > C.kcap) { atomicExch(C.stats + ST_OVERFLOW, 1ull); return 0; }      // (after the warp collectives)
 #pragma unroll
     for (int a = 0; a < KS; ++a) {
         ninv[a] = 0.0; nw[a] = 0.0;
@@ -633,31 +472,12 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
                 if (b < kr) { d2 = fma(-l, l, d2); t = fma(-l, nw[b], t); }
             }
         }
-        if (d2 > SSPS_PIVOT_TOL * gjj) {
-            jinv = 1.0 / sqrt(d2); jw = t * jinv;
-            q_new = fma(jw, jw, q_new);
-        } else if (d2 != d2 || gjj != gjj) {
-            jinv = __longlong_as_double(0x7ff8000000000000LL); jw = jinv; q_new = jinv;
-        }
+        chol_pivot(d2, gjj, t, jinv, jw, q_new);
     }
     const double ip_new = __ldg(P.yty + child) - P.shrink * q_new;
-
-    // ---- screened acceptance test: accept iff log(u) < alpha ----
-    const float lgu = fast_lg2((float)d.u_acc);
     const float lg_new = fast_lg2((float)ip_new);
-    const double hn = 0.5 * P.dn;
-    const double base = ((dprior - fwd) + bwd) - 0.5 * (double)(kn - k) * P.log1pn;
-    const double diff = SSPS_LN2 * ((double)lgu + hn * ((double)lg_new - (double)L.lg_ip)) - base;
-    const double marg = 1.2e-6 * ((double)fabsf(lgu) + 1.0 + hn * ((double)(fabsf(lg_new) + fabsf(L.lg_ip)) + 2.0)) + 1e-9 * fabs(base) + 1e-6;
-    bool accept = diff < 0.0;
-    if (!(d.u_acc > 1e-30 && fabs(diff) > marg)) {        // too close (or NaN): the reference-order fp64 test
-        ++n_t1;
-        const double lml_cur = -0.5 * (double)k * P.log1pn - 0.5 * P.dn * log(L.ip);
-        const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
-        const double w = dprior + (lml_new - lml_cur);
-        const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
-        accept = log(d.u_acc) < alpha;
-    }
+    const bool accept = mh_accept(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1);
+
     if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
         int t = 0;
 #pragma unroll
@@ -669,18 +489,21 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     }
     if (!accept) return 0;
 
-    if (kn > KS) {      // outgrows shared memory
-        L = small_to_big(P, child, L, S, C, p, j_add, j_rem, rel_now);
-        return 1;
-    }
-    // ---- accepted: tallies / change points, then factor and id list back to shared memory ----
+    // ---- accepted: tallies / change points ----
     if (has_rem) {
-        const int credit = rel_now - (int)(S.W(p) >> 16);
+        const int credit = rel_now - (int)(idw[(p < KS) ? p : 0] >> 16);
         if (credit > 0) C.cnt_row[j_rem] += (uint32_t)credit;
         if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
     }
     if (has_add && C.pev && L.n_pev < C.pev_cap)
         C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
+    L.somc = (L.somc - omc_rem) + omc_add;
+    L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
+    if (kn > KS) {      // an arrival that outgrows shared memory (k == KS, pure add): the warp moves the lane to the BIG tier
+        L.mode = MODE_PROMOTE; L.pend_j = j_add;
+        return 1;
+    }
+    // ---- factor and id list back to shared memory ----
     int rj = 0;
 #pragma unroll
     for (int a = 0; a < KS; ++a) {
@@ -707,22 +530,313 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
         S.set_rank(kr, rj);
     }
     L.k = kn;
-    L.somc = (L.somc - omc_rem) + omc_add;
-    L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
     return 1;
 }
 #undef NL
 
-// lanes whose set lives in the arena
+// ------------------------------------------------------------------------------------------------
+// BIG tier, warp-cooperative.  All arguments are warp-uniform; every lane of the warp must call.
+//
+// coop_eval: q of the proposed set of the lane that owns B (remove arrival position p if p < k,
+// then append j_add if >= 0).  The new rows p .. kn-1, in the proposed set's coordinates, are left
+// in the warp's scratch factor B.s (entries >= p of the rows >= p, 1/d and w; entries < p of those
+// rows are the cached entries of old row a + 1).
+//
+// The rows after a removal are refactorised RIGHT-LOOKING: once column b is final, every lane
+// subtracts its product from the entries (a, c), c > b, it owns.  Each entry therefore receives
+// the terms of  G_ac - sum_m l_am l_cm  in ascending m through fma -- the operation order of the
+// row-by-row factorisation in orc_lml_chol -- so the result is the same bit pattern.
+// ------------------------------------------------------------------------------------------------
+__device__ __noinline__ double coop_eval(const SspsDev& P, const double* __restrict__ Ri, const BigRef B, const int k, const int p,
+                                         const int j_add, const int lane) {
+    const int V = P.V;
+    double* __restrict__ f = B.f; double* __restrict__ s = B.s;
+    double* __restrict__ fw = B.fw(); double* __restrict__ sw = B.sw();
+    double q = 0.0;
+    const int pm = p < k ? p : k;
+    for (int m = 0; m < pm; ++m) { const double wm = fw[m]; q = fma(wm, wm, q); }
+    const int kr = p < k ? k - 1 : k;
+
+    if (p < kr) {
+        // partial sums over the unchanged columns m < p (row a of the reduced set = old row a + 1); pseudo-column a + 1 = t_a
+        for (int a = p; a < kr; ++a) {
+            const int ja = B.id(a + 1);
+            const double* __restrict__ Ga = P.G + (size_t)ja * V;
+            const double* __restrict__ ra = f + SSPS_TRI(a + 1);
+            for (int c = p + lane; c <= a + 1; c += 32) {
+                if (c <= a) {
+                    double x = __ldg(Ga + B.id(c + 1));
+                    const double* __restrict__ rc = f + SSPS_TRI(c + 1);
+                    for (int m = 0; m < p; ++m) x = fma(-ra[m], rc[m], x);
+                    s[SSPS_TRI(a) + c] = x;
+                } else {
+                    double x = __ldg(Ri + ja);
+                    for (int m = 0; m < p; ++m) x = fma(-ra[m], fw[m], x);
+                    sw[a] = x;
+                }
+            }
+        }
+        __syncwarp();
+        for (int b = p; b < kr; ++b) {
+            const int jb = B.id(b + 1);
+            const double gbb = __ldg(P.G + (size_t)jb * V + jb);
+            const double d2 = s[SSPS_TRI(b) + b], t = sw[b];
+            double inv, wb;
+            chol_pivot(d2, gbb, t, inv, wb, q);
+            __syncwarp();                               // every lane has read d2 and t
+            if (lane == 0) { s[SSPS_TRI(b) + b] = inv; sw[b] = wb; }
+            for (int a = b + 1 + lane; a < kr; a += 32) {     // column b and its share of t_a
+                const double l = s[SSPS_TRI(a) + b] * inv;
+                s[SSPS_TRI(a) + b] = l;
+                sw[a] = fma(-l, wb, sw[a]);
+            }
+            __syncwarp();
+            for (int a = b + 1; a < kr; ++a) {                // trailing entries (a, c), b < c <= a
+                const double lab = s[SSPS_TRI(a) + b];
+                for (int c = b + 1 + lane; c <= a; c += 32) s[SSPS_TRI(a) + c] = fma(-lab, s[SSPS_TRI(c) + b], s[SSPS_TRI(a) + c]);
+            }
+            __syncwarp();
+        }
+    }
+
+    if (j_add >= 0) {       // the appended row kr: forward substitution, lane owns columns lane + 32 u
+        const double* __restrict__ Gj = P.G + (size_t)j_add * V;
+        const double gjj = __ldg(Gj + j_add);
+        double d2 = gjj, t = __ldg(Ri + j_add);
+        double sc[SSPS_KU];
+#pragma unroll
+        for (int u = 0; u < SSPS_KU; ++u) {
+            const int c = lane + 32 * u;
+            sc[u] = (c < kr) ? __ldg(Gj + B.id(c < p ? c : c + 1)) : 0.0;
+        }
+        for (int b = 0; b < kr; ++b) {
+            const double invb = (b < p) ? f[SSPS_TRI(b) + b] : s[SSPS_TRI(b) + b];
+            const double wb = (b < p) ? fw[b] : sw[b];
+            double mine = sc[0];
+#pragma unroll
+            for (int u = 1; u < SSPS_KU; ++u) if ((b >> 5) == u) mine = sc[u];
+            const double l = __shfl_sync(SSPS_FULL, mine * invb, b & 31);
+            d2 = fma(-l, l, d2);
+            t = fma(-l, wb, t);
+            if (lane == (b & 31)) s[SSPS_TRI(kr) + b] = l;
+#pragma unroll
+            for (int u = 0; u < SSPS_KU; ++u) {
+                const int c = lane + 32 * u;
+                if (c > b && c < kr) {
+                    const double lcb = (c < p) ? f[SSPS_TRI(c) + b] : ((b < p) ? f[SSPS_TRI(c + 1) + b] : s[SSPS_TRI(c) + b]);
+                    sc[u] = fma(-l, lcb, sc[u]);
+                }
+            }
+        }
+        double inv, wj;
+        chol_pivot(d2, gjj, t, inv, wj, q);
+        if (lane == 0) { s[SSPS_TRI(kr) + kr] = inv; sw[kr] = wj; }
+    }
+    __syncwarp();
+    return q;
+}
+
+// accepted: fold the scratch rows into the lane's factor and edit its id list (ranks).  Returns the new size.
+__device__ __noinline__ int coop_commit(const BigRef B, const int k, const int p, const int j_add, const int rel_now, const int lane) {
+    double* __restrict__ f = B.f; double* __restrict__ s = B.s;
+    double* __restrict__ fw = B.fw(); double* __restrict__ sw = B.sw();
+    int kr = k;
+    if (p < k) {
+        const int rp = (int)B.r[p];
+        __syncwarp();
+        for (int base = 0; base < k; base += 32) {      // id list: drop slot p, close the rank gap
+            const int b = base + lane;
+            uint32_t wv = 0; int rv = 0;
+            if (b < k - 1) {
+                const int from = b >= p ? b + 1 : b;
+                wv = B.w[from]; rv = (int)B.r[from];
+                rv -= (rv > rp) ? 1 : 0;
+            }
+            __syncwarp();
+            if (b < k - 1) { B.w[b] = wv; B.r[b] = (uint16_t)rv; }
+            __syncwarp();
+        }
+        for (int a = p; a < k - 1; ++a) {               // row a <- entries < p of old row a + 1, the recomputed rest
+            double v[SSPS_KU];
+#pragma unroll
+            for (int u = 0; u < SSPS_KU; ++u) {
+                const int m = lane + 32 * u;
+                v[u] = (m <= a) ? ((m < p) ? f[SSPS_TRI(a + 1) + m] : s[SSPS_TRI(a) + m]) : 0.0;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int u = 0; u < SSPS_KU; ++u) {
+                const int m = lane + 32 * u;
+                if (m <= a) f[SSPS_TRI(a) + m] = v[u];
+            }
+            if (lane == 0) fw[a] = sw[a];
+            __syncwarp();
+        }
+        kr = k - 1;
+    }
+    if (j_add >= 0) {
+        for (int m = lane; m <= kr; m += 32) f[SSPS_TRI(kr) + m] = s[SSPS_TRI(kr) + m];
+        if (lane == 0) fw[kr] = sw[kr];
+        int rj = 0;
+        for (int base = 0; base < kr; base += 32) {
+            const int b = base + lane;
+            const bool lt = b < kr && B.id(b) < j_add;
+            rj += __popc(__ballot_sync(SSPS_FULL, lt));
+            if (b < kr && !lt) B.r[b] = (uint16_t)(B.r[b] + 1);
+        }
+        if (lane == 0) { B.w[kr] = (uint32_t)j_add | ((uint32_t)rel_now << 16); B.r[kr] = (uint16_t)rj; }
+        ++kr;
+    }
+    __syncwarp();
+    return kr;
+}
+
+// factor of lane B's current set from its id list (task start): append the rows in arrival order
+__device__ __noinline__ double coop_build(const SspsDev& P, const double* __restrict__ Ri, const BigRef B, const int k, const int lane) {
+    double q = 0.0;
+    for (int a = 0; a < k; ++a) {
+        q = coop_eval(P, Ri, B, a, a, B.id(a), lane);
+        for (int m = lane; m <= a; m += 32) B.f[SSPS_TRI(a) + m] = B.s[SSPS_TRI(a) + m];
+        if (lane == 0) B.fw()[a] = B.sw()[a];
+        __syncwarp();
+    }
+    return q;
+}
+
+// lane `src` leaves the BIG tier (|S| <= SSPS_KS): ids, ranks and factor into its shared-memory slots
+__device__ __forceinline__ void coop_demote(const BigRef B, const SmallAcc Ss, const int k, const int lane) {
+    for (int e = lane; e < SSPS_TRI(k); e += 32) Ss.d[e * SSPS_BLOCK] = B.f[e];
+    if (lane < k) { Ss.Wv(lane) = B.fw()[lane]; Ss.W(lane) = B.w[lane]; Ss.set_rank(lane, (int)B.r[lane]); }
+    __syncwarp();
+}
+// lane `src` enters the BIG tier with its current SMALL state
+__device__ __forceinline__ void coop_promote(const BigRef B, const SmallAcc Ss, const int k, const int lane) {
+    for (int e = lane; e < SSPS_TRI(k); e += 32) B.f[e] = Ss.d[e * SSPS_BLOCK];
+    if (lane < k) { B.fw()[lane] = Ss.Wv(lane); B.w[lane] = Ss.W(lane); B.r[lane] = (uint16_t)Ss.rank(lane); }
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------------
+// The parent-set move of the BIG lanes of a warp (mask `bigm`), one lane at a time with the whole
+// warp working on it, then the pending arrivals into the tier (mask `pend`).  Same draws, same
+// decisions, same bits as the SMALL path and the oracle: smart_proposal + smart_involution + Gen.mh.
+// acc_kn (per lane): accepted | |S'| << 1 of this lane's move.
+// ------------------------------------------------------------------------------------------------
 template <bool VERIFY>
-__device__ __noinline__ Lane big_move(const SspsDev& P, const int child, const StepDraws& d, Lane L, const SmallAcc& S, const KCtx& C,
-                                      const int rel_now, int* acc_kn) {
-    unsigned n_t1 = 0; int kn = 0;
-    const int acc = parent_move<BigAcc, VERIFY>(P, child, d, L, C.big, S, C, rel_now, n_t1, kn);
-    if (n_t1) atomicAdd(C.stats + ST_TIER1, 1ull);
-    atomicAdd(C.stats + ST_BIG_STEPS, 1ull);
-    if (acc && L.k <= SSPS_KS) L = lane_settle(P, child, L, S, C);     // back into shared memory
-    *acc_kn = acc | (kn << 1);
+__device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const StepDraws& d, Lane L, const SmallAcc& S, const KCtx& C,
+                                       const int rel_now, unsigned bigm, unsigned pend, int* acc_kn) {
+    const int lane = threadIdx.x & 31;
+    const int V = P.V;
+    const double* __restrict__ Ri = P.R + (size_t)V * child;
+    unsigned n_big = 0, n_t1 = 0;
+    while (bigm) {
+        const int src = __ffs(bigm) - 1;
+        bigm &= bigm - 1;
+        const BigRef B = C.big(src);
+        int action = 0, a_ord = 0, r_ord = 0;
+        if (lane == src) select_move(P, child, L.k, d, action, a_ord, r_ord);
+        const int k = __shfl_sync(SSPS_FULL, L.k, src);
+        action = __shfl_sync(SSPS_FULL, action, src);
+        a_ord = __shfl_sync(SSPS_FULL, a_ord, src);
+        r_ord = __shfl_sync(SSPS_FULL, r_ord, src);
+        const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
+        int j_add = -1, j_rem = -1, p = k;
+        if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
+            int c = 0;
+            for (int base = 0; base < k; base += 32) {
+                const int b = base + lane;
+                c += __popc(__ballot_sync(SSPS_FULL, b < k && B.id(b) - (int)B.r[b] < a_ord));
+            }
+            j_add = a_ord - 1 + c;
+        }
+        if (has_rem) {          // the r-th element of the sorted list
+            for (int base = 0; base < k; base += 32) {
+                const int b = base + lane;
+                const unsigned hit = __ballot_sync(SSPS_FULL, b < k && (int)B.r[b] == r_ord - 1);
+                if (hit) p = base + __ffs(hit) - 1;
+            }
+            j_rem = B.id(p);
+        }
+        const int kn = k + (has_add ? 1 : 0) - (has_rem ? 1 : 0);
+        ++n_big;
+        if (kn > C.kcap) {
+            if (lane == src) { atomicExch(C.stats + ST_OVERFLOW, 1ull); *acc_kn = kn << 1; }
+            continue;
+        }
+        const double q_new = coop_eval(P, Ri, B, k, p, j_add, lane);
+        int acc = 0;
+        if (lane == src) {
+            double fwd, bwd;
+            move_ratio(P, child, k, action, fwd, bwd);
+            const double* __restrict__ omc_i = P.omc + (size_t)V * child;
+            double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
+            if (has_add) { omc_add = __ldg(omc_i + j_add); dprior = -L.lam * omc_add; }
+            if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
+            const double ip_new = __ldg(P.yty + child) - P.shrink * q_new;
+            const float lg_new = fast_lg2((float)ip_new);
+            acc = mh_accept(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1) ? 1 : 0;
+            if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
+                int t = 0;
+                for (int b = 0; b < k; ++b) if (b != p) C.xs.T(t++) = (uint16_t)B.id(b);
+                if (j_add >= 0) C.xs.T(t++) = (uint16_t)j_add;
+                const double lml_ref = score_set(P, child, C.xs, t, nullptr);
+                const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
+                if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
+            }
+            if (acc) {
+                if (has_rem) {
+                    const int credit = rel_now - (int)(B.w[p] >> 16);
+                    if (credit > 0) C.cnt_row[j_rem] += (uint32_t)credit;
+                    if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
+                }
+                if (has_add && C.pev && L.n_pev < C.pev_cap)
+                    C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
+                L.somc = (L.somc - omc_rem) + omc_add;
+                L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
+                L.k = kn;
+                if (kn <= SSPS_KS) L.mode = MODE_SMALL;
+            }
+            *acc_kn = acc | (kn << 1);
+        }
+        acc = __shfl_sync(SSPS_FULL, acc, src);
+        if (acc) {
+            coop_commit(B, k, p, j_add, rel_now, lane);
+            if (kn <= SSPS_KS) coop_demote(B, S.of_lane(src - lane), kn, lane);
+        }
+    }
+    while (pend) {          // arrivals accepted by small_move with |S'| = SSPS_KS + 1
+        const int src = __ffs(pend) - 1;
+        pend &= pend - 1;
+        const BigRef B = C.big(src);
+        const int j_add = __shfl_sync(SSPS_FULL, L.pend_j, src);
+        coop_promote(B, S.of_lane(src - lane), SSPS_KS, lane);
+        coop_eval(P, Ri, B, SSPS_KS, SSPS_KS, j_add, lane);
+        coop_commit(B, SSPS_KS, SSPS_KS, j_add, rel_now, lane);
+        if (lane == src) { L.mode = MODE_BIG; L.k = SSPS_KS + 1; }
+    }
+    if (lane == 0) {
+        if (n_big) atomicAdd(C.stats + ST_BIG_STEPS, (unsigned long long)n_big);
+    }
+    if (n_t1) atomicAdd(C.stats + ST_TIER1, (unsigned long long)n_t1);
+    return L;
+}
+
+// task start: ids of the lanes are in place (SMALL: shared memory, BIG: arena); build the factors
+__device__ __noinline__ Lane task_settle(const SspsDev& P, const int child, Lane L, const bool live, const SmallAcc& S, const KCtx& C) {
+    const int lane = threadIdx.x & 31;
+    const double* __restrict__ Ri = P.R + (size_t)P.V * child;
+    if (live) {
+        L.somc = sorted_somc(P, child, L.mode, S, C.big(lane), C.xs, L.k);
+        if (L.mode == MODE_SMALL) lane_set_q(P, child, L, small_build(P, Ri, S, L.k));
+    }
+    unsigned bigm = __ballot_sync(SSPS_FULL, live && L.mode == MODE_BIG);
+    while (bigm) {
+        const int src = __ffs(bigm) - 1;
+        bigm &= bigm - 1;
+        const int k = __shfl_sync(SSPS_FULL, L.k, src);
+        const double q = coop_build(P, Ri, C.big(src), k, lane);
+        if (lane == src) lane_set_q(P, child, L, q);
+    }
     return L;
 }
 
@@ -737,12 +851,16 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
     SmallAcc S;
     S.d = smem_d + threadIdx.x;
-    S.w = (uint32_t*)(smem_d + (size_t)2 * SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK) + threadIdx.x;
-    S.r = (uint8_t*)((uint32_t*)(smem_d + (size_t)2 * SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK) + (size_t)SSPS_KS * SSPS_BLOCK) + threadIdx.x;
+    S.w = (uint32_t*)(smem_d + (size_t)SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK) + threadIdx.x;
+    S.r = (uint8_t*)((uint32_t*)(smem_d + (size_t)SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK) + (size_t)SSPS_KS * SSPS_BLOCK) + threadIdx.x;
     KCtx C;
-    C.big.d = prm.big_d + gtid; C.big.w = prm.big_w + gtid; C.big.r = prm.big_r + gtid; C.big.stride = prm.stride; C.big.kcap = prm.kcap;
+    C.kcap = prm.kcap;
+    C.big_d0 = prm.big_d + (size_t)(gtid - lane) * SSPS_ROWLEN(prm.kcap);
+    C.big_w0 = prm.big_w + (size_t)(gtid - lane) * prm.kcap;
+    C.big_r0 = prm.big_r + (size_t)(gtid - lane) * prm.kcap;
+    C.scr = prm.scr_d + (size_t)(gtid >> 5) * SSPS_ROWLEN(prm.kcap);
     C.xs.d = prm.x_d + gtid; C.xs.t = prm.x_t + gtid; C.xs.stride = prm.stride; C.xs.kcap = prm.kcap;
-    C.kcap = prm.kcap; C.stats = prm.stats; C.pev_cap = prm.pev_cap;
+    C.stats = prm.stats; C.pev_cap = prm.pev_cap;
     const int V = P.V;
     const int thin = prm.thinning;
 
@@ -752,36 +870,51 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
     for (;;) {
         int task = 0;
         if (lane == 0) task = atomicAdd(prm.task_counter, 1);
-        task = __shfl_sync(0xffffffffu, task, 0);
+        task = __shfl_sync(SSPS_FULL, task, 0);
         if (task >= prm.n_tasks) break;
         const long long t_start = clock64();
         const int i = __ldg(prm.order + task / prm.n_slabs);
         const int chain = (task % prm.n_slabs) * 32 + lane;
-        if (chain < st.n_chains) {
-            const size_t sidx = (size_t)i * st.nch_pad + chain;
-            const size_t mc = (size_t)chain * V + i;
-            C.cnt_row = st.counts + mc * V;
-            C.pev = prm.pev ? prm.pev + mc * prm.pev_cap : nullptr;
-            Lane L;
-            L.k = st.k[sidx]; L.lam = st.lambda[sidx]; L.n_pev = 0;
-            L.q = 0.0; L.ip = 0.0; L.lg_ip = 0.f; L.somc = 0.0; L.mode = MODE_BIG;
-            bool dead = false;
-            if (L.k > prm.kcap) { atomicExch(prm.stats + ST_OVERFLOW, 1ull); dead = true; }
-            else {
+        bool live = chain < st.n_chains;
+        const size_t sidx = (size_t)i * st.nch_pad + (live ? chain : 0);
+        const size_t mc = (size_t)(live ? chain : 0) * V + i;
+        C.cnt_row = st.counts + mc * V;
+        C.pev = prm.pev ? prm.pev + mc * prm.pev_cap : nullptr;
+        Lane L;
+        L.k = 0; L.lam = 0.0; L.n_pev = 0; L.pend_j = -1;
+        L.q = 0.0; L.ip = 0.0; L.lg_ip = 0.f; L.somc = 0.0; L.nrmf = 0.0; L.mode = MODE_SMALL;
+        if (live) {
+            L.k = st.k[sidx]; L.lam = st.lambda[sidx];
+            if (L.k > prm.kcap) { atomicExch(prm.stats + ST_OVERFLOW, 1ull); live = false; L.k = 0; }
+        }
+        if (live) {     // parent list: id | rank << 16, arrival order
+            if (L.k <= SSPS_KS) {
                 for (int a = 0; a < L.k; ++a) {
-                    const uint32_t sl = slot_ref(st, V, i, a, chain);       // id | rank << 16, arrival order
-                    C.big.W(a) = sl & 0xffffu; C.big.set_rank(a, (int)(sl >> 16));
+                    const uint32_t sl = slot_ref(st, V, i, a, chain);
+                    S.W(a) = sl & 0xffffu; S.set_rank(a, (int)(sl >> 16));
                 }
-                L = lane_settle(P, i, L, S, C);
+            } else {
+                L.mode = MODE_BIG;
+                const BigRef B = C.big(lane);
+                for (int a = 0; a < L.k; ++a) {
+                    const uint32_t sl = slot_ref(st, V, i, a, chain);
+                    B.w[a] = sl & 0xffffu; B.r[a] = (uint16_t)(sl >> 16);
+                }
             }
-            L.nrmf = normaliser_fast(P, i, L.lam);
-            const float lmarg = __ldg(P.lam_margin + i);
-            double lam_sum = 0.0, lam_sq = 0.0, lam_logged = L.lam;
-            int n_lev = 0;
-            DrawCarry cy; cy.valid = 0; cy.z = 0.f; cy.w = 0u;
+        }
+        __syncwarp();
+        L = task_settle(P, i, L, live, S, C);
+        float lmarg = 0.f;
+        if (live) { L.nrmf = normaliser_fast(P, i, L.lam); lmarg = __ldg(P.lam_margin + i); }
+        double lam_sum = 0.0, lam_sq = 0.0, lam_logged = L.lam;
+        int n_lev = 0;
+        DrawCarry cy; cy.valid = 0; cy.z = 0.f; cy.w = 0u;
 
-            for (int l = 1; l <= prm.n_local && !dead; ++l) {
-                const StepDraws d = src.get(chain, i, (uint64_t)(prm.sweep0 + l), (int64_t)(l - 1), cy);
+        for (int l = 1; l <= prm.n_local; ++l) {
+            StepDraws d;
+            d.z = 0.0; d.u_lam = 0.5; d.u_act = 0.5; d.u_add = 0.5; d.u_rem = 0.5; d.u_acc = 0.5;
+            if (live) {
+                d = src.get(chain, i, (uint64_t)(prm.sweep0 + l), (int64_t)(l - 1), cy);
 
                 // ---------------- lambda move (lambda_vec_proposal + Gen.mh) ----------------
                 const double lam_new = L.lam + P.sigma * d.z;
@@ -793,23 +926,28 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
                     bool acc = diff < 0.0;
                     if (!(d.u_lam > 1e-30 && fabs(diff) > (double)lmarg + 1.2e-6 * ((double)fabsf(lgu) + 1.0) + 1e-9 * fabs(w))) {
                         ++s_lx;
-                        write_sorted(L.mode, S, C.big, C.xs, L.k);
+                        write_sorted(L.mode, S, C.big(lane), C.xs, L.k);
                         acc = lambda_exact_decide(P, i, C.xs, L.k, L.lam, lam_new, d.u_lam) != 0;
                     }
                     if (acc) { L.lam = lam_new; L.nrmf = nrm_new; ++s_accl; }
                 }
+            }
 
-                // ---------------- parent-set move ----------------
-                const int rel_now = ceil_div_i(l, thin) - 1;   // recorded samples of this launch that precede the change
+            // ---------------- parent-set move ----------------
+            const int rel_now = ceil_div_i(l, thin) - 1;   // recorded samples of this launch that precede the change
+            int acc_kn = 0;
+            const unsigned bigm = __ballot_sync(SSPS_FULL, live && L.mode == MODE_BIG);
+            const unsigned smallm = __ballot_sync(SSPS_FULL, live && L.mode == MODE_SMALL);
+            if (live && L.mode == MODE_SMALL) {
                 int kn = 0;
-                if (L.mode == MODE_SMALL) {
-                    s_accp += (unsigned)small_move<VERIFY>(P, i, d, L, S, C, rel_now, s_t1, kn);
-                } else {
-                    int acc_kn = 0;
-                    L = big_move<VERIFY>(P, i, d, L, S, C, rel_now, &acc_kn);
-                    s_accp += (unsigned)(acc_kn & 1);
-                    kn = acc_kn >> 1;
-                }
+                const int acc = small_move<VERIFY>(P, i, d, L, S, C, rel_now, smallm, s_t1, kn);
+                acc_kn = acc | (kn << 1);
+            }
+            const unsigned pend = __ballot_sync(SSPS_FULL, L.mode == MODE_PROMOTE);
+            if (bigm | pend) L = big_phase<VERIFY>(P, i, d, L, S, C, rel_now, bigm, pend, &acc_kn);
+            if (live) {
+                const int kn = acc_kn >> 1;
+                s_accp += (unsigned)(acc_kn & 1);
                 ++s_prop;
                 s_k += (unsigned)kn;
                 s_f3 += (unsigned long long)kn * kn * kn + 6ull * kn * kn + 6ull * kn;
@@ -829,22 +967,23 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
                     }
                 }
             }
+        }
 
-            // flush lazy tallies, store the parent list (arrival order, id | rank << 16) and the state
-            if (!dead) {
-                const int rec_local = prm.n_local / thin;
-                for (int b = 0; b < L.k; ++b) {
-                    const uint32_t slw = L.mode == MODE_SMALL ? S.W(b) : C.big.W(b);
-                    const int rk = L.mode == MODE_SMALL ? S.rank(b) : C.big.rank(b);
-                    const int credit = rec_local - (int)(slw >> 16);
-                    if (credit > 0) C.cnt_row[slw & 0xffffu] += (uint32_t)credit;
-                    slot_ref(st, V, i, b, chain) = (slw & 0xffffu) | ((uint32_t)rk << 16);
-                }
-                st.k[sidx] = L.k;
-                st.lambda[sidx] = L.lam;
-                st.lam_sum[mc] += lam_sum;
-                st.lam_sq[mc] += lam_sq;
+        // flush lazy tallies, store the parent list (arrival order, id | rank << 16) and the state
+        if (live) {
+            const int rec_local = prm.n_local / thin;
+            const BigRef B = C.big(lane);
+            for (int b = 0; b < L.k; ++b) {
+                const uint32_t slw = L.mode == MODE_SMALL ? S.W(b) : B.w[b];
+                const int rk = L.mode == MODE_SMALL ? S.rank(b) : (int)B.r[b];
+                const int credit = rec_local - (int)(slw >> 16);
+                if (credit > 0) C.cnt_row[slw & 0xffffu] += (uint32_t)credit;
+                slot_ref(st, V, i, b, chain) = (slw & 0xffffu) | ((uint32_t)rk << 16);
             }
+            st.k[sidx] = L.k;
+            st.lambda[sidx] = L.lam;
+            st.lam_sum[mc] += lam_sum;
+            st.lam_sq[mc] += lam_sq;
             if (prm.pev_n) prm.pev_n[mc] = L.n_pev;
             if (prm.lev_n) prm.lev_n[mc] = n_lev;
         }
@@ -858,7 +997,7 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
         unsigned long long x = v[e];
-        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(SSPS_FULL, x, o);
         if (lane == 0 && x) atomicAdd(prm.stats + slot[e], x);
     }
 }

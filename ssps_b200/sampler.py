@@ -292,6 +292,13 @@ class Sampler:
         check(self._L.ssps_get_khist(self._h, _l(h), length))
         return h
 
+    def vertex_cost(self):
+        """(warp cycles per vertex in the last MH launch, mean in-degree per vertex now)."""
+        c = np.zeros(self.V, dtype=np.int64)
+        k = np.zeros(self.V, dtype=np.int32)
+        check(self._L.ssps_get_vertex_cost(self._h, _l(c), k.ctypes.data_as(C.POINTER(C.c_int32))))
+        return c, k / 1000.0
+
     def measure_fp64_peak(self) -> float:
         t = C.c_double(0.0)
         check(self._L.ssps_measure_fp64_peak(self._h, C.byref(t)))

@@ -25,3 +25,10 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
                  (st.n_lambda_exact - prev.n_lambda_exact) / dp, (st.n_accepted - prev.n_accepted) / dp,
                  (st.n_lambda_accepted - prev.n_lambda_accepted) / dp, st.n_mismatch))
         prev = st
+    cost, mk = s.vertex_cost()
+    n_slabs = (C + 31) // 32
+    o = np.argsort(-cost)
+    print("kernel ms last rep / launches:", dms, "grid warps:", "?")
+    print("per-task mean cycles by vertex (top 12):", [(int(i), round(cost[i] / n_slabs / 1e6, 3), round(float(mk[i]), 2)) for i in o[:12]])
+    print("sum task Mcycles %.1f, max task Mcycles %.3f, median %.3f" % (cost.sum() / 1e6, cost.max() / n_slabs / 1e6, np.median(cost) / n_slabs / 1e6))
+    print("mean indeg hist:", np.histogram(mk, bins=[0, 1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 16, 32, 64])[0])
