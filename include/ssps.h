@@ -98,6 +98,7 @@ typedef struct {
     int64_t n_tier1;            /* parent-set tests whose fp32 screening was too close: redone in reference order, fp64 logs */
     int64_t n_lambda_exact;     /* lambda-move tests redone in reference order */
     int64_t n_big_steps;        /* proposals of lanes whose factor lives in the global-memory tier (|S| > 6) */
+    int64_t big_cycles;         /* warp cycles spent in the cooperative global-memory tier (clock64, summed over warps) */
     int64_t n_mismatch;         /* verify = 1 only: proposals whose cached-factor score differs from the from-scratch
                                    score of the same parent list by even one bit (must be 0) */
 } ssps_run_stats;

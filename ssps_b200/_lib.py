@@ -37,7 +37,7 @@ class RunStats(C.Structure):
         ("n_accepted", C.c_int64), ("n_lambda_accepted", C.c_int64), ("sum_k", C.c_int64),
         ("algorithmic_flops", C.c_double), ("algorithmic_bytes", C.c_double), ("kernel_ms", C.c_double),
         ("kernel_launches", C.c_int64), ("mh_launches", C.c_int64),
-        ("n_tier1", C.c_int64), ("n_lambda_exact", C.c_int64), ("n_big_steps", C.c_int64), ("n_mismatch", C.c_int64),
+        ("n_tier1", C.c_int64), ("n_lambda_exact", C.c_int64), ("n_big_steps", C.c_int64), ("big_cycles", C.c_int64), ("n_mismatch", C.c_int64),
     ]
 
 

@@ -1109,6 +1109,7 @@ int ssps_get_stats(ssps_handle* h, ssps_run_stats* out) {
         out->algorithmic_bytes = 8.0 * (double)st[ST_BYTES];
         out->n_tier1 = (int64_t)st[ST_TIER1]; out->n_big_steps = (int64_t)st[ST_BIG_STEPS];
         out->n_lambda_exact = (int64_t)st[ST_LAM_EXACT]; out->n_mismatch = (int64_t)st[ST_MISMATCH];
+        out->big_cycles = (int64_t)st[ST_BIG_CYCLES];
         out->kernel_ms = h->kernel_ms;
         out->mh_launches = h->mh_launches;
     }

@@ -50,7 +50,7 @@
 enum { MODE_SMALL = 0, MODE_BIG = 1, MODE_PROMOTE = 2 };
 // stats slots (unsigned long long each)
 enum { ST_ACCP = 0, ST_ACCL = 1, ST_SUMK = 2, ST_F3 = 3, ST_BYTES = 4, ST_OVERFLOW = 5, ST_PROP = 6, ST_TIER1 = 7,
-       ST_MISMATCH = 10, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_N = 16 };
+       ST_MISMATCH = 10, ST_BIG_CYCLES = 11, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_N = 16 };
 
 __device__ __forceinline__ float fast_lg2(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float fast_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -729,6 +729,7 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
     const int V = P.V;
     const double* __restrict__ Ri = P.R + (size_t)V * child;
     unsigned n_big = 0, n_t1 = 0;
+    const long long t_in = clock64();
     while (bigm) {
         const int src = __ffs(bigm) - 1;
         bigm &= bigm - 1;
@@ -816,6 +817,7 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
     }
     if (lane == 0) {
         if (n_big) atomicAdd(C.stats + ST_BIG_STEPS, (unsigned long long)n_big);
+        atomicAdd(C.stats + ST_BIG_CYCLES, (unsigned long long)(clock64() - t_in));
     }
     if (n_t1) atomicAdd(C.stats + ST_TIER1, (unsigned long long)n_t1);
     return L;

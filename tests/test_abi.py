@@ -32,7 +32,7 @@ def test_header_symbols_are_exported_and_bound():
 def test_struct_layouts_match_header():
     from ssps_b200 import _lib
     assert ctypes.sizeof(_lib.Config) == 56
-    assert ctypes.sizeof(_lib.RunStats) == 88 + 4 * 8
+    assert ctypes.sizeof(_lib.RunStats) == 88 + 5 * 8
 
 
 def test_no_cpu_fallback_without_gpu():

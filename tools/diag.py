@@ -11,7 +11,7 @@ S = int(sys.argv[3]) if len(sys.argv) > 3 else 400
 verify = len(sys.argv) > 4 and sys.argv[4] == "verify"
 T = int(os.environ.get("DIAG_T", "8"))
 ds, xm, xp = make_workload(V, T, 4)
-with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), verify=verify) as s:
+with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), verify=verify, collect_khist=bool(os.environ.get('DIAG_KHIST'))) as s:
     s.set_data(xm, xp, ds.prior_graph)
     s.generate(C, seed=1)
     prev = s.stats()
@@ -24,6 +24,8 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
               % (rep, dp / (dms * 1e-3), (st.n_tier1 - prev.n_tier1) / dp, (st.n_big_steps - prev.n_big_steps) / dp,
                  (st.n_lambda_exact - prev.n_lambda_exact) / dp, (st.n_accepted - prev.n_accepted) / dp,
                  (st.n_lambda_accepted - prev.n_lambda_accepted) / dp, st.n_mismatch))
+        print("      big: %.0f cycles per big lane-step, %.3f of all task cycles" % ((st.big_cycles - prev.big_cycles) / max(st.n_big_steps - prev.n_big_steps, 1),
+              (st.big_cycles - prev.big_cycles) / max(float(s.vertex_cost()[0].sum()) * 4, 1.0)))
         prev = st
     cost, mk = s.vertex_cost()
     n_slabs = (C + 31) // 32
@@ -32,3 +34,5 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
     print("per-task mean cycles by vertex (top 12):", [(int(i), round(cost[i] / n_slabs / 1e6, 3), round(float(mk[i]), 2)) for i in o[:12]])
     print("sum task Mcycles %.1f, max task Mcycles %.3f, median %.3f" % (cost.sum() / 1e6, cost.max() / n_slabs / 1e6, np.median(cost) / n_slabs / 1e6))
     print("mean indeg hist:", np.histogram(mk, bins=[0, 1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 16, 32, 64])[0])
+    if os.environ.get('DIAG_KHIST'):
+        print("khist:", s.khist(40).tolist())
