@@ -119,8 +119,8 @@ struct ssps_handle {
     int mh_grid = 0;
     size_t mh_smem = 0;
     DevBuf<double> big_d, scr_d, x_d;   // BIG-tier factors (per resident thread), scratch factor (per resident warp), verify scratch
-    DevBuf<uint32_t> big_w;
-    DevBuf<uint16_t> big_r, x_t;
+    DevBuf<uint32_t> big_w, scr_w;
+    DevBuf<uint16_t> big_r, scr_r, x_t;
     DevBuf<int> task_counter, order;
     DevBuf<unsigned long long> stats, khist, vcost;
     bool have_cost = false;         // vcost holds the previous launch's per-vertex cycles
@@ -488,8 +488,7 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     st.lam_sum = h->lam_sum.p; st.lam_sq = h->lam_sq.p;
 
     // persistent MH grid: as many CTAs as stay resident, never more than there are warp-tasks
-    h->mh_smem = (size_t)SSPS_ROWLEN(SSPS_KS) * sizeof(double) * SSPS_BLOCK + (size_t)SSPS_KS * sizeof(uint32_t) * SSPS_BLOCK
-               + (size_t)SSPS_KS * SSPS_BLOCK;
+    h->mh_smem = SSPS_SMEM_BYTES;
     int occ = 1 << 30;
     {
         // Shared memory holds only the SMALL-tier factors; what the carve-out leaves is L1 for the G / R / move
@@ -519,7 +518,7 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     const size_t nthreads = (size_t)h->mh_grid * SSPS_BLOCK;
     const size_t kc = (size_t)h->kcap;
     CK(h->big_d.alloc(nthreads * SSPS_ROWLEN(kc)));
-    CK(h->scr_d.alloc(nthreads / 32 * SSPS_ROWLEN(kc)));
+    CK(h->scr_d.alloc(nthreads / 32 * SSPS_ROWLEN(kc))); CK(h->scr_w.alloc(nthreads / 32 * kc)); CK(h->scr_r.alloc(nthreads / 32 * kc));
     CK(h->big_w.alloc(nthreads * kc));
     CK(h->big_r.alloc(nthreads * kc));
     CK(h->x_d.alloc(h->cfg.verify ? nthreads * (SSPS_TRI(kc) + kc) : 1));
@@ -714,7 +713,7 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
         prm.n_tasks = V * prm.n_slabs;
         prm.task_counter = h->task_counter.p;
         prm.order = h->order.p; prm.vcost = h->vcost.p;
-        prm.big_d = h->big_d.p; prm.big_w = h->big_w.p; prm.big_r = h->big_r.p; prm.scr_d = h->scr_d.p;
+        prm.big_d = h->big_d.p; prm.big_w = h->big_w.p; prm.big_r = h->big_r.p; prm.scr_d = h->scr_d.p; prm.scr_w = h->scr_w.p; prm.scr_r = h->scr_r.p;
         prm.x_d = h->x_d.p; prm.x_t = h->x_t.p;
         prm.kcap = h->kcap; prm.stride = h->mh_grid * SSPS_BLOCK;
         prm.stats = h->stats.p;

@@ -155,13 +155,31 @@ struct SmallAcc {   // shared memory, element-major: [e][thread]
     __device__ __forceinline__ SmallAcc of_lane(int delta) const { SmallAcc o; o.d = d + delta; o.w = w + delta; o.r = r + delta; return o; }
 };
 
-// one lane's block of the BIG arena + the warp's scratch factor (same shape, proposed set's coordinates)
+// one lane's block of the BIG arena (the master copy of its ids, ranks and factor between steps)
 struct BigRef {
-    double* f; double* s; uint32_t* w; uint16_t* r; int kcap;
+    double* f; uint32_t* w; uint16_t* r; int kcap;
     __device__ __forceinline__ double* fw() const { return f + SSPS_TRI(kcap); }
-    __device__ __forceinline__ double* sw() const { return s + SSPS_TRI(kcap); }
     __device__ __forceinline__ int id(int a) const { return (int)(w[a] & 0xffffu); }
 };
+
+// The warp's working copy of ONE lane's BIG-tier state while the warp works on it: shared memory when
+// the proposed set fits SSPS_KST rows, else the warp's global scratch.  A move is applied to the copy
+// in place (ids, ranks, factor -> those of the proposed set); the copy is written back only on accept.
+#ifndef SSPS_KST
+#define SSPS_KST 32
+#endif
+struct Stage {
+    double* t;          // factor rows, TRI-packed, 1/d in the diagonal slots
+    double* tw;         // w
+    uint32_t* id;       // id | rel << 16, arrival order
+    uint16_t* rk;       // sorted rank
+    __device__ __forceinline__ int idof(int a) const { return (int)(id[a] & 0xffffu); }
+};
+
+// dynamic shared memory of one CTA: SMALL-tier slots of every thread + one Stage per warp
+#define SSPS_SMEM_DOUBLES (SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK + (SSPS_BLOCK / 32) * SSPS_ROWLEN(SSPS_KST))
+#define SSPS_SMEM_WORDS (SSPS_KS * SSPS_BLOCK + (SSPS_BLOCK / 32) * SSPS_KST)
+#define SSPS_SMEM_BYTES ((size_t)SSPS_SMEM_DOUBLES * 8 + (size_t)SSPS_SMEM_WORDS * 4 + (size_t)(SSPS_BLOCK / 32) * SSPS_KST * 2 + (size_t)SSPS_KS * SSPS_BLOCK)
 
 struct Lane {
     double lam, somc, q, ip, nrmf;   // nrmf: screening value of the prior normaliser at lam
@@ -177,8 +195,10 @@ struct MhParams {
     int* task_counter;
     const int* order;        // vertices, most expensive first
     unsigned long long* vcost;   // per-vertex cycles of this launch
-    // BIG tier: per resident thread [gtid][ROWLEN(kcap)] / [gtid][kcap]; scratch factor per resident warp
-    double* big_d; uint32_t* big_w; uint16_t* big_r; double* scr_d;
+    // BIG tier: per resident thread [gtid][ROWLEN(kcap)] / [gtid][kcap]; the same per resident WARP as the
+    // working copy of sets too large for the shared-memory Stage
+    double* big_d; uint32_t* big_w; uint16_t* big_r;
+    double* scr_d; uint32_t* scr_w; uint16_t* scr_r;
     double* x_d; uint16_t* x_t;                            // per-thread id lists (x_t) and from-scratch scorer scratch (x_d: verify only)
     int kcap; int stride;
     unsigned long long* stats;
@@ -190,7 +210,7 @@ struct MhParams {
 
 struct KCtx {       // per-lane pointers
     double* big_d0; uint32_t* big_w0; uint16_t* big_r0;    // arena block of lane 0 of this warp
-    double* scr;                                           // this warp's scratch factor
+    Stage st_smem, st_glob;                                // this warp's working copies
     Scratch xs;
     uint32_t* cnt_row;     // counts + mc * V
     uint32_t* pev;         // pev + mc * pev_cap (nullable)
@@ -198,10 +218,11 @@ struct KCtx {       // per-lane pointers
     unsigned long long* stats;
     __device__ __forceinline__ BigRef big(int ln) const {
         BigRef b;
-        b.f = big_d0 + (size_t)ln * SSPS_ROWLEN(kcap); b.s = scr;
+        b.f = big_d0 + (size_t)ln * SSPS_ROWLEN(kcap);
         b.w = big_w0 + (size_t)ln * kcap; b.r = big_r0 + (size_t)ln * kcap; b.kcap = kcap;
         return b;
     }
+    __device__ __forceinline__ Stage stage(int rows) const { return rows <= SSPS_KST ? st_smem : st_glob; }
 };
 
 __device__ __forceinline__ int ceil_div_i(int a, int b) { return (a + b - 1) / b; }
@@ -537,183 +558,159 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
 // ------------------------------------------------------------------------------------------------
 // BIG tier, warp-cooperative.  All arguments are warp-uniform; every lane of the warp must call.
 //
-// coop_eval: q of the proposed set of the lane that owns B (remove arrival position p if p < k,
-// then append j_add if >= 0).  The new rows p .. kn-1, in the proposed set's coordinates, are left
-// in the warp's scratch factor B.s (entries >= p of the rows >= p, 1/d and w; entries < p of those
-// rows are the cached entries of old row a + 1).
+// The warp copies the lane's state into its Stage, applies the move to the copy IN PLACE
+// (ids_remove / fac_remove, then fac_append / ids_append) and reads off q of the proposed set; the
+// copy goes back to the arena only if the move is accepted.
 //
 // The rows after a removal are refactorised RIGHT-LOOKING: once column b is final, every lane
 // subtracts its product from the entries (a, c), c > b, it owns.  Each entry therefore receives
 // the terms of  G_ac - sum_m l_am l_cm  in ascending m through fma -- the operation order of the
 // row-by-row factorisation in orc_lml_chol -- so the result is the same bit pattern.
 // ------------------------------------------------------------------------------------------------
-__device__ __noinline__ double coop_eval(const SspsDev& P, const double* __restrict__ Ri, const BigRef B, const int k, const int p,
-                                         const int j_add, const int lane) {
-    const int V = P.V;
-    double* __restrict__ f = B.f; double* __restrict__ s = B.s;
-    double* __restrict__ fw = B.fw(); double* __restrict__ sw = B.sw();
-    double q = 0.0;
-    const int pm = p < k ? p : k;
-    for (int m = 0; m < pm; ++m) { const double wm = fw[m]; q = fma(wm, wm, q); }
-    const int kr = p < k ? k - 1 : k;
+__device__ __forceinline__ void stage_load(const Stage T, const BigRef B, const int k, const int lane) {
+    for (int e = lane; e < SSPS_TRI(k); e += 32) T.t[e] = B.f[e];
+    const double* __restrict__ fw = B.fw();
+    for (int a = lane; a < k; a += 32) { T.tw[a] = fw[a]; T.id[a] = B.w[a]; T.rk[a] = B.r[a]; }
+    __syncwarp();
+}
+__device__ __forceinline__ void stage_store(const Stage T, const BigRef B, const int k, const int lane) {
+    for (int e = lane; e < SSPS_TRI(k); e += 32) B.f[e] = T.t[e];
+    double* __restrict__ fw = B.fw();
+    for (int a = lane; a < k; a += 32) { fw[a] = T.tw[a]; B.w[a] = T.id[a]; B.r[a] = T.rk[a]; }
+    __syncwarp();
+}
+// SMALL-tier slots of one lane <-> Stage
+__device__ __forceinline__ void stage_from_small(const Stage T, const SmallAcc Ss, const int k, const int lane) {
+    for (int e = lane; e < SSPS_TRI(k); e += 32) T.t[e] = Ss.d[e * SSPS_BLOCK];
+    if (lane < k) { T.tw[lane] = Ss.Wv(lane); T.id[lane] = Ss.W(lane); T.rk[lane] = (uint16_t)Ss.rank(lane); }
+    __syncwarp();
+}
+__device__ __forceinline__ void stage_to_small(const Stage T, const SmallAcc Ss, const int k, const int lane) {
+    for (int e = lane; e < SSPS_TRI(k); e += 32) Ss.d[e * SSPS_BLOCK] = T.t[e];
+    if (lane < k) { Ss.Wv(lane) = T.tw[lane]; Ss.W(lane) = T.id[lane]; Ss.set_rank(lane, (int)T.rk[lane]); }
+    __syncwarp();
+}
 
-    if (p < kr) {
-        // partial sums over the unchanged columns m < p (row a of the reduced set = old row a + 1); pseudo-column a + 1 = t_a
-        for (int a = p; a < kr; ++a) {
-            const int ja = B.id(a + 1);
-            const double* __restrict__ Ga = P.G + (size_t)ja * V;
-            const double* __restrict__ ra = f + SSPS_TRI(a + 1);
-            for (int c = p + lane; c <= a + 1; c += 32) {
-                if (c <= a) {
-                    double x = __ldg(Ga + B.id(c + 1));
-                    const double* __restrict__ rc = f + SSPS_TRI(c + 1);
-                    for (int m = 0; m < p; ++m) x = fma(-ra[m], rc[m], x);
-                    s[SSPS_TRI(a) + c] = x;
-                } else {
-                    double x = __ldg(Ri + ja);
-                    for (int m = 0; m < p; ++m) x = fma(-ra[m], fw[m], x);
-                    sw[a] = x;
-                }
-            }
+// id list: drop arrival slot p, close the gap in the sorted ranks
+__device__ __forceinline__ void ids_remove(const Stage T, const int k, const int p, const int lane) {
+    const int rp = (int)T.rk[p];
+    __syncwarp();
+    for (int base = 0; base < k; base += 32) {
+        const int b = base + lane;
+        uint32_t wv = 0; int rv = 0;
+        if (b < k - 1) {
+            const int from = b >= p ? b + 1 : b;
+            wv = T.id[from]; rv = (int)T.rk[from];
+            rv -= (rv > rp) ? 1 : 0;
         }
         __syncwarp();
-        for (int b = p; b < kr; ++b) {
-            const int jb = B.id(b + 1);
-            const double gbb = __ldg(P.G + (size_t)jb * V + jb);
-            const double d2 = s[SSPS_TRI(b) + b], t = sw[b];
-            double inv, wb;
-            chol_pivot(d2, gbb, t, inv, wb, q);
-            __syncwarp();                               // every lane has read d2 and t
-            if (lane == 0) { s[SSPS_TRI(b) + b] = inv; sw[b] = wb; }
-            for (int a = b + 1 + lane; a < kr; a += 32) {     // column b and its share of t_a
-                const double l = s[SSPS_TRI(a) + b] * inv;
-                s[SSPS_TRI(a) + b] = l;
-                sw[a] = fma(-l, wb, sw[a]);
+        if (b < k - 1) { T.id[b] = wv; T.rk[b] = (uint16_t)rv; }
+        __syncwarp();
+    }
+}
+// id list: parent j arrives in slot kr
+__device__ __forceinline__ void ids_append(const Stage T, const int kr, const int j, const int rel_now, const int lane) {
+    int rj = 0;
+    for (int base = 0; base < kr; base += 32) {
+        const int b = base + lane;
+        const bool lt = b < kr && T.idof(b) < j;
+        rj += __popc(__ballot_sync(SSPS_FULL, lt));
+        if (b < kr && !lt) T.rk[b] = (uint16_t)(T.rk[b] + 1);
+    }
+    if (lane == 0) { T.id[kr] = (uint32_t)j | ((uint32_t)rel_now << 16); T.rk[kr] = (uint16_t)rj; }
+    __syncwarp();
+}
+
+// Factor after the removal of arrival slot p of k (T.id already holds the reduced list, the rows are
+// still in the old coordinates).  q_in = sum of w_m^2 over m < p; returns q over all k - 1 rows.
+__device__ __noinline__ double fac_remove(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int k, const int p,
+                                          double q, const int lane) {
+    const int V = P.V, kr = k - 1;
+    double* t = T.t; double* tw = T.tw;
+    if (p >= kr) return q;
+    // rows a >= p keep the entries m < p of old row a + 1 (lane m carries column m through all rows: no cross-lane hazard)
+    for (int a = p; a < kr; ++a)
+        for (int m = lane; m < p; m += 32) t[SSPS_TRI(a) + m] = t[SSPS_TRI(a + 1) + m];
+    __syncwarp();
+    // partial sums over the unchanged columns m < p; pseudo-column a + 1 = t_a
+    for (int a = p; a < kr; ++a) {
+        const int ja = T.idof(a);
+        const double* __restrict__ Ga = P.G + (size_t)ja * V;
+        double* ra = t + SSPS_TRI(a);
+        for (int c = p + lane; c <= a + 1; c += 32) {
+            if (c <= a) {
+                double x = __ldg(Ga + T.idof(c));
+                const double* rc = t + SSPS_TRI(c);
+                for (int m = 0; m < p; ++m) x = fma(-ra[m], rc[m], x);
+                ra[c] = x;
+            } else {
+                double x = __ldg(Ri + ja);
+                for (int m = 0; m < p; ++m) x = fma(-ra[m], tw[m], x);
+                tw[a] = x;
             }
-            __syncwarp();
-            for (int a = b + 1; a < kr; ++a) {                // trailing entries (a, c), b < c <= a
-                const double lab = s[SSPS_TRI(a) + b];
-                for (int c = b + 1 + lane; c <= a; c += 32) s[SSPS_TRI(a) + c] = fma(-lab, s[SSPS_TRI(c) + b], s[SSPS_TRI(a) + c]);
-            }
-            __syncwarp();
         }
     }
+    __syncwarp();
+    for (int b = p; b < kr; ++b) {
+        const int jb = T.idof(b);
+        const double gbb = __ldg(P.G + (size_t)jb * V + jb);
+        const double d2 = t[SSPS_TRI(b) + b], tb = tw[b];
+        double inv, wb;
+        chol_pivot(d2, gbb, tb, inv, wb, q);
+        __syncwarp();                               // every lane has read d2 and t_b
+        if (lane == 0) { t[SSPS_TRI(b) + b] = inv; tw[b] = wb; }
+        for (int a = b + 1 + lane; a < kr; a += 32) {     // column b and its share of t_a
+            const double l = t[SSPS_TRI(a) + b] * inv;
+            t[SSPS_TRI(a) + b] = l;
+            tw[a] = fma(-l, wb, tw[a]);
+        }
+        __syncwarp();
+        for (int a = b + 1; a < kr; ++a) {                // trailing entries (a, c), b < c <= a
+            const double lab = t[SSPS_TRI(a) + b];
+            for (int c = b + 1 + lane; c <= a; c += 32) t[SSPS_TRI(a) + c] = fma(-lab, t[SSPS_TRI(c) + b], t[SSPS_TRI(a) + c]);
+        }
+        __syncwarp();
+    }
+    return q;
+}
 
-    if (j_add >= 0) {       // the appended row kr: forward substitution, lane owns columns lane + 32 u
-        const double* __restrict__ Gj = P.G + (size_t)j_add * V;
-        const double gjj = __ldg(Gj + j_add);
-        double d2 = gjj, t = __ldg(Ri + j_add);
-        double sc[SSPS_KU];
+// Row kr of the factor: parent j appended to the kr rows in the Stage (forward substitution, lane owns
+// columns lane + 32 u).  Returns q + w_kr^2.
+__device__ __noinline__ double fac_append(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int kr, const int j,
+                                          double q, const int lane) {
+    const int V = P.V;
+    double* t = T.t; double* tw = T.tw;
+    const double* __restrict__ Gj = P.G + (size_t)j * V;
+    const double gjj = __ldg(Gj + j);
+    double d2 = gjj, tj = __ldg(Ri + j);
+    double sc[SSPS_KU];
+#pragma unroll
+    for (int u = 0; u < SSPS_KU; ++u) {
+        const int c = lane + 32 * u;
+        sc[u] = (c < kr) ? __ldg(Gj + T.idof(c)) : 0.0;
+    }
+    double* rj = t + SSPS_TRI(kr);
+    for (int b = 0; b < kr; ++b) {
+        const double invb = t[SSPS_TRI(b) + b];
+        const double wb = tw[b];
+        double mine = sc[0];
+#pragma unroll
+        for (int u = 1; u < SSPS_KU; ++u) if ((b >> 5) == u) mine = sc[u];
+        const double l = __shfl_sync(SSPS_FULL, mine * invb, b & 31);
+        d2 = fma(-l, l, d2);
+        tj = fma(-l, wb, tj);
+        if (lane == (b & 31)) rj[b] = l;
 #pragma unroll
         for (int u = 0; u < SSPS_KU; ++u) {
             const int c = lane + 32 * u;
-            sc[u] = (c < kr) ? __ldg(Gj + B.id(c < p ? c : c + 1)) : 0.0;
+            if (c > b && c < kr) sc[u] = fma(-l, t[SSPS_TRI(c) + b], sc[u]);
         }
-        for (int b = 0; b < kr; ++b) {
-            const double invb = (b < p) ? f[SSPS_TRI(b) + b] : s[SSPS_TRI(b) + b];
-            const double wb = (b < p) ? fw[b] : sw[b];
-            double mine = sc[0];
-#pragma unroll
-            for (int u = 1; u < SSPS_KU; ++u) if ((b >> 5) == u) mine = sc[u];
-            const double l = __shfl_sync(SSPS_FULL, mine * invb, b & 31);
-            d2 = fma(-l, l, d2);
-            t = fma(-l, wb, t);
-            if (lane == (b & 31)) s[SSPS_TRI(kr) + b] = l;
-#pragma unroll
-            for (int u = 0; u < SSPS_KU; ++u) {
-                const int c = lane + 32 * u;
-                if (c > b && c < kr) {
-                    const double lcb = (c < p) ? f[SSPS_TRI(c) + b] : ((b < p) ? f[SSPS_TRI(c + 1) + b] : s[SSPS_TRI(c) + b]);
-                    sc[u] = fma(-l, lcb, sc[u]);
-                }
-            }
-        }
-        double inv, wj;
-        chol_pivot(d2, gjj, t, inv, wj, q);
-        if (lane == 0) { s[SSPS_TRI(kr) + kr] = inv; sw[kr] = wj; }
     }
+    double inv, wj;
+    chol_pivot(d2, gjj, tj, inv, wj, q);
+    if (lane == 0) { rj[kr] = inv; tw[kr] = wj; }
     __syncwarp();
     return q;
-}
-
-// accepted: fold the scratch rows into the lane's factor and edit its id list (ranks).  Returns the new size.
-__device__ __noinline__ int coop_commit(const BigRef B, const int k, const int p, const int j_add, const int rel_now, const int lane) {
-    double* __restrict__ f = B.f; double* __restrict__ s = B.s;
-    double* __restrict__ fw = B.fw(); double* __restrict__ sw = B.sw();
-    int kr = k;
-    if (p < k) {
-        const int rp = (int)B.r[p];
-        __syncwarp();
-        for (int base = 0; base < k; base += 32) {      // id list: drop slot p, close the rank gap
-            const int b = base + lane;
-            uint32_t wv = 0; int rv = 0;
-            if (b < k - 1) {
-                const int from = b >= p ? b + 1 : b;
-                wv = B.w[from]; rv = (int)B.r[from];
-                rv -= (rv > rp) ? 1 : 0;
-            }
-            __syncwarp();
-            if (b < k - 1) { B.w[b] = wv; B.r[b] = (uint16_t)rv; }
-            __syncwarp();
-        }
-        for (int a = p; a < k - 1; ++a) {               // row a <- entries < p of old row a + 1, the recomputed rest
-            double v[SSPS_KU];
-#pragma unroll
-            for (int u = 0; u < SSPS_KU; ++u) {
-                const int m = lane + 32 * u;
-                v[u] = (m <= a) ? ((m < p) ? f[SSPS_TRI(a + 1) + m] : s[SSPS_TRI(a) + m]) : 0.0;
-            }
-            __syncwarp();
-#pragma unroll
-            for (int u = 0; u < SSPS_KU; ++u) {
-                const int m = lane + 32 * u;
-                if (m <= a) f[SSPS_TRI(a) + m] = v[u];
-            }
-            if (lane == 0) fw[a] = sw[a];
-            __syncwarp();
-        }
-        kr = k - 1;
-    }
-    if (j_add >= 0) {
-        for (int m = lane; m <= kr; m += 32) f[SSPS_TRI(kr) + m] = s[SSPS_TRI(kr) + m];
-        if (lane == 0) fw[kr] = sw[kr];
-        int rj = 0;
-        for (int base = 0; base < kr; base += 32) {
-            const int b = base + lane;
-            const bool lt = b < kr && B.id(b) < j_add;
-            rj += __popc(__ballot_sync(SSPS_FULL, lt));
-            if (b < kr && !lt) B.r[b] = (uint16_t)(B.r[b] + 1);
-        }
-        if (lane == 0) { B.w[kr] = (uint32_t)j_add | ((uint32_t)rel_now << 16); B.r[kr] = (uint16_t)rj; }
-        ++kr;
-    }
-    __syncwarp();
-    return kr;
-}
-
-// factor of lane B's current set from its id list (task start): append the rows in arrival order
-__device__ __noinline__ double coop_build(const SspsDev& P, const double* __restrict__ Ri, const BigRef B, const int k, const int lane) {
-    double q = 0.0;
-    for (int a = 0; a < k; ++a) {
-        q = coop_eval(P, Ri, B, a, a, B.id(a), lane);
-        for (int m = lane; m <= a; m += 32) B.f[SSPS_TRI(a) + m] = B.s[SSPS_TRI(a) + m];
-        if (lane == 0) B.fw()[a] = B.sw()[a];
-        __syncwarp();
-    }
-    return q;
-}
-
-// lane `src` leaves the BIG tier (|S| <= SSPS_KS): ids, ranks and factor into its shared-memory slots
-__device__ __forceinline__ void coop_demote(const BigRef B, const SmallAcc Ss, const int k, const int lane) {
-    for (int e = lane; e < SSPS_TRI(k); e += 32) Ss.d[e * SSPS_BLOCK] = B.f[e];
-    if (lane < k) { Ss.Wv(lane) = B.fw()[lane]; Ss.W(lane) = B.w[lane]; Ss.set_rank(lane, (int)B.r[lane]); }
-    __syncwarp();
-}
-// lane `src` enters the BIG tier with its current SMALL state
-__device__ __forceinline__ void coop_promote(const BigRef B, const SmallAcc Ss, const int k, const int lane) {
-    for (int e = lane; e < SSPS_TRI(k); e += 32) B.f[e] = Ss.d[e * SSPS_BLOCK];
-    if (lane < k) { B.fw()[lane] = Ss.Wv(lane); B.w[lane] = Ss.W(lane); B.r[lane] = (uint16_t)Ss.rank(lane); }
-    __syncwarp();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -741,30 +738,49 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
         a_ord = __shfl_sync(SSPS_FULL, a_ord, src);
         r_ord = __shfl_sync(SSPS_FULL, r_ord, src);
         const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
-        int j_add = -1, j_rem = -1, p = k;
-        if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
-            int c = 0;
-            for (int base = 0; base < k; base += 32) {
-                const int b = base + lane;
-                c += __popc(__ballot_sync(SSPS_FULL, b < k && B.id(b) - (int)B.r[b] < a_ord));
-            }
-            j_add = a_ord - 1 + c;
-        }
-        if (has_rem) {          // the r-th element of the sorted list
-            for (int base = 0; base < k; base += 32) {
-                const int b = base + lane;
-                const unsigned hit = __ballot_sync(SSPS_FULL, b < k && (int)B.r[b] == r_ord - 1);
-                if (hit) p = base + __ffs(hit) - 1;
-            }
-            j_rem = B.id(p);
-        }
         const int kn = k + (has_add ? 1 : 0) - (has_rem ? 1 : 0);
         ++n_big;
         if (kn > C.kcap) {
             if (lane == src) { atomicExch(C.stats + ST_OVERFLOW, 1ull); *acc_kn = kn << 1; }
             continue;
         }
-        const double q_new = coop_eval(P, Ri, B, k, p, j_add, lane);
+        const Stage T = C.stage(k + 1);
+        stage_load(T, B, k, lane);
+        int j_add = -1, j_rem = -1, p = k;
+        uint32_t w_rem = 0;
+        if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
+            int c = 0;
+            for (int base = 0; base < k; base += 32) {
+                const int b = base + lane;
+                c += __popc(__ballot_sync(SSPS_FULL, b < k && T.idof(b) - (int)T.rk[b] < a_ord));
+            }
+            j_add = a_ord - 1 + c;
+        }
+        if (has_rem) {          // the r-th element of the sorted list
+            for (int base = 0; base < k; base += 32) {
+                const int b = base + lane;
+                const unsigned hit = __ballot_sync(SSPS_FULL, b < k && (int)T.rk[b] == r_ord - 1);
+                if (hit) p = base + __ffs(hit) - 1;
+            }
+            w_rem = T.id[p];
+            j_rem = (int)(w_rem & 0xffffu);
+        }
+        // ---- apply the move to the working copy ----
+        double q_new = 0.0;
+        {
+            const int pm = p < k ? p : k;
+            for (int m = 0; m < pm; ++m) { const double wm = T.tw[m]; q_new = fma(wm, wm, q_new); }
+        }
+        int kr = k;
+        if (has_rem) {
+            ids_remove(T, k, p, lane);
+            q_new = fac_remove(P, Ri, T, k, p, q_new, lane);
+            kr = k - 1;
+        }
+        if (has_add) {
+            q_new = fac_append(P, Ri, T, kr, j_add, q_new, lane);
+            ids_append(T, kr, j_add, rel_now, lane);
+        }
         int acc = 0;
         if (lane == src) {
             double fwd, bwd;
@@ -777,16 +793,14 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
             const float lg_new = fast_lg2((float)ip_new);
             acc = mh_accept(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1) ? 1 : 0;
             if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
-                int t = 0;
-                for (int b = 0; b < k; ++b) if (b != p) C.xs.T(t++) = (uint16_t)B.id(b);
-                if (j_add >= 0) C.xs.T(t++) = (uint16_t)j_add;
-                const double lml_ref = score_set(P, child, C.xs, t, nullptr);
+                for (int b = 0; b < kn; ++b) C.xs.T(b) = (uint16_t)T.idof(b);
+                const double lml_ref = score_set(P, child, C.xs, kn, nullptr);
                 const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
                 if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
             }
             if (acc) {
                 if (has_rem) {
-                    const int credit = rel_now - (int)(B.w[p] >> 16);
+                    const int credit = rel_now - (int)(w_rem >> 16);
                     if (credit > 0) C.cnt_row[j_rem] += (uint32_t)credit;
                     if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
                 }
@@ -801,18 +815,19 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
         }
         acc = __shfl_sync(SSPS_FULL, acc, src);
         if (acc) {
-            coop_commit(B, k, p, j_add, rel_now, lane);
-            if (kn <= SSPS_KS) coop_demote(B, S.of_lane(src - lane), kn, lane);
+            if (kn <= SSPS_KS) stage_to_small(T, S.of_lane(src - lane), kn, lane);
+            else stage_store(T, B, kn, lane);
         }
     }
     while (pend) {          // arrivals accepted by small_move with |S'| = SSPS_KS + 1
         const int src = __ffs(pend) - 1;
         pend &= pend - 1;
-        const BigRef B = C.big(src);
         const int j_add = __shfl_sync(SSPS_FULL, L.pend_j, src);
-        coop_promote(B, S.of_lane(src - lane), SSPS_KS, lane);
-        coop_eval(P, Ri, B, SSPS_KS, SSPS_KS, j_add, lane);
-        coop_commit(B, SSPS_KS, SSPS_KS, j_add, rel_now, lane);
+        const Stage T = C.stage(SSPS_KS + 1);
+        stage_from_small(T, S.of_lane(src - lane), SSPS_KS, lane);
+        fac_append(P, Ri, T, SSPS_KS, j_add, 0.0, lane);
+        ids_append(T, SSPS_KS, j_add, rel_now, lane);
+        stage_store(T, C.big(src), SSPS_KS + 1, lane);
         if (lane == src) { L.mode = MODE_BIG; L.k = SSPS_KS + 1; }
     }
     if (lane == 0) {
@@ -832,11 +847,17 @@ __device__ __noinline__ Lane task_settle(const SspsDev& P, const int child, Lane
         if (L.mode == MODE_SMALL) lane_set_q(P, child, L, small_build(P, Ri, S, L.k));
     }
     unsigned bigm = __ballot_sync(SSPS_FULL, live && L.mode == MODE_BIG);
-    while (bigm) {
+    while (bigm) {          // rows appended in arrival order
         const int src = __ffs(bigm) - 1;
         bigm &= bigm - 1;
         const int k = __shfl_sync(SSPS_FULL, L.k, src);
-        const double q = coop_build(P, Ri, C.big(src), k, lane);
+        const BigRef B = C.big(src);
+        const Stage T = C.stage(k);
+        for (int a = lane; a < k; a += 32) { T.id[a] = B.w[a]; T.rk[a] = B.r[a]; }
+        __syncwarp();
+        double q = 0.0;
+        for (int a = 0; a < k; ++a) q = fac_append(P, Ri, T, a, T.idof(a), q, lane);
+        stage_store(T, B, k, lane);
         if (lane == src) lane_set_q(P, child, L, q);
     }
     return L;
@@ -852,15 +873,28 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
     const int lane = threadIdx.x & 31;
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
     SmallAcc S;
-    S.d = smem_d + threadIdx.x;
-    S.w = (uint32_t*)(smem_d + (size_t)SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK) + threadIdx.x;
-    S.r = (uint8_t*)((uint32_t*)(smem_d + (size_t)SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK) + (size_t)SSPS_KS * SSPS_BLOCK) + threadIdx.x;
+    double* stage_smem_t; uint32_t* stage_smem_id; uint16_t* stage_smem_rk;
+    {   // [SMALL d | Stage d per warp | SMALL w | Stage id per warp | Stage rk per warp | SMALL r]
+        const int wic = threadIdx.x >> 5;
+        double* const stage_d = smem_d + (size_t)SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK;
+        uint32_t* const words = (uint32_t*)(smem_d + SSPS_SMEM_DOUBLES);
+        uint16_t* const halves = (uint16_t*)(words + SSPS_SMEM_WORDS);
+        uint8_t* const bytes = (uint8_t*)(halves + (SSPS_BLOCK / 32) * SSPS_KST);
+        S.d = smem_d + threadIdx.x;
+        S.w = words + threadIdx.x;
+        S.r = bytes + threadIdx.x;
+        stage_smem_t = stage_d + (size_t)wic * SSPS_ROWLEN(SSPS_KST);
+        stage_smem_id = words + SSPS_KS * SSPS_BLOCK + wic * SSPS_KST;
+        stage_smem_rk = halves + wic * SSPS_KST;
+    }
     KCtx C;
     C.kcap = prm.kcap;
     C.big_d0 = prm.big_d + (size_t)(gtid - lane) * SSPS_ROWLEN(prm.kcap);
     C.big_w0 = prm.big_w + (size_t)(gtid - lane) * prm.kcap;
     C.big_r0 = prm.big_r + (size_t)(gtid - lane) * prm.kcap;
-    C.scr = prm.scr_d + (size_t)(gtid >> 5) * SSPS_ROWLEN(prm.kcap);
+    C.st_smem.t = stage_smem_t; C.st_smem.tw = stage_smem_t + SSPS_TRI(SSPS_KST); C.st_smem.id = stage_smem_id; C.st_smem.rk = stage_smem_rk;
+    C.st_glob.t = prm.scr_d + (size_t)(gtid >> 5) * SSPS_ROWLEN(prm.kcap); C.st_glob.tw = C.st_glob.t + SSPS_TRI(prm.kcap);
+    C.st_glob.id = prm.scr_w + (size_t)(gtid >> 5) * prm.kcap; C.st_glob.rk = prm.scr_r + (size_t)(gtid >> 5) * prm.kcap;
     C.xs.d = prm.x_d + gtid; C.xs.t = prm.x_t + gtid; C.xs.stride = prm.stride; C.xs.kcap = prm.kcap;
     C.stats = prm.stats; C.pev_cap = prm.pev_cap;
     const int V = P.V;
