@@ -121,7 +121,8 @@ struct ssps_handle {
     DevBuf<double> big_d, scr_d, x_d;   // BIG-tier factors (per resident thread), scratch factor (per resident warp), verify scratch
     DevBuf<uint32_t> big_w, scr_w;
     DevBuf<uint16_t> big_r, scr_r, x_t;
-    DevBuf<int> task_counter, order;
+    DevBuf<int> task_counter, order, task_start, task_split;
+    DevBuf<double> task_est;
     DevBuf<unsigned long long> stats, khist, vcost;
     bool have_cost = false;         // vcost holds the previous launch's per-vertex cycles
 
@@ -525,6 +526,12 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     CK(h->x_t.alloc(nthreads * 2 * kc));
     CK(h->task_counter.alloc(1));
     CK(h->order.alloc(V)); CK(h->vcost.alloc(V));
+    CK(h->task_start.alloc((size_t)V + 1)); CK(h->task_split.alloc(V)); CK(h->task_est.alloc(V));
+    {
+        std::vector<int> ones((size_t)V, 1);
+        CK(cudaMemcpyAsync(h->task_split.p, ones.data(), sizeof(int) * (size_t)V, cudaMemcpyHostToDevice, s));
+        CK(cudaStreamSynchronize(s));
+    }
     CK(h->stats.alloc(ST_N)); CK(h->khist.alloc(64));
     CK(cudaMemsetAsync(h->stats.p, 0, h->stats.bytes(), s));
     CK(cudaMemsetAsync(h->khist.p, 0, h->khist.bytes(), s));
@@ -712,7 +719,7 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
         prm.n_slabs = h->nch_pad / 32;
         prm.n_tasks = V * prm.n_slabs;
         prm.task_counter = h->task_counter.p;
-        prm.order = h->order.p; prm.vcost = h->vcost.p;
+        prm.order = h->order.p; prm.vcost = h->vcost.p; prm.start = h->task_start.p; prm.split = h->task_split.p; prm.V = V;
         prm.big_d = h->big_d.p; prm.big_w = h->big_w.p; prm.big_r = h->big_r.p; prm.scr_d = h->scr_d.p; prm.scr_w = h->scr_w.p; prm.scr_r = h->scr_r.p;
         prm.x_d = h->x_d.p; prm.x_t = h->x_t.p;
         prm.kcap = h->kcap; prm.stride = h->mh_grid * SSPS_BLOCK;
@@ -723,12 +730,13 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
             prm.pev = h->pev.p; prm.pev_n = h->pev_n.p; prm.pev_cap = h->pev_cap;
             prm.lev_val = h->lev_val.p; prm.lev_idx = h->lev_idx.p; prm.lev_n = h->lev_n.p; prm.lev_cap = h->lev_cap;
         }
-        // task order: vertices by the cycles they cost in the previous launch (first launch: by in-degree)
+        // task schedule: from the cycles every vertex cost in the previous launch (first launch: by in-degree, no split)
         if (!h->have_cost) {
             cost_from_state_kernel<<<V, 128, 0, h->stream>>>(h->st, V, h->vcost.p);
             CKS(launch_ok(h, "cost_from_state"));
         }
-        order_kernel<<<div_up((size_t)V, 128), 128, 0, h->stream>>>(h->vcost.p, V, h->order.p);
+        schedule_kernel<<<1, 256, 0, h->stream>>>(h->vcost.p, V, prm.n_slabs, h->mh_grid * (SSPS_BLOCK / 32), h->have_cost ? 1 : 0,
+                                                  h->task_split.p, h->order.p, h->task_start.p, h->task_est.p);
         CKS(launch_ok(h, "order"));
         CK(cudaMemsetAsync(h->vcost.p, 0, h->vcost.bytes(), h->stream));
         h->have_cost = true;

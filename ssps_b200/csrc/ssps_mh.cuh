@@ -193,7 +193,10 @@ struct MhParams {
     int thinning;
     int n_tasks, n_slabs;
     int* task_counter;
-    const int* order;        // vertices, most expensive first
+    const int* order;        // vertices, longest tasks first
+    const int* start;        // first task id per rank; start[V] = number of tasks
+    const int* split;        // per vertex: warps per slab (1, 2, 4, 8)
+    int V;
     unsigned long long* vcost;   // per-vertex cycles of this launch
     // BIG tier: per resident thread [gtid][ROWLEN(kcap)] / [gtid][kcap]; the same per resident WARP as the
     // working copy of sets too large for the shared-memory Stage
@@ -907,11 +910,16 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
         int task = 0;
         if (lane == 0) task = atomicAdd(prm.task_counter, 1);
         task = __shfl_sync(SSPS_FULL, task, 0);
-        if (task >= prm.n_tasks) break;
+        if (task >= __ldg(prm.start + prm.V)) break;
         const long long t_start = clock64();
-        const int i = __ldg(prm.order + task / prm.n_slabs);
-        const int chain = (task % prm.n_slabs) * 32 + lane;
-        bool live = chain < st.n_chains;
+        int lo = 0, hi = prm.V - 1;                     // the rank whose task range holds `task`
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (__ldg(prm.start + mid) <= task) lo = mid; else hi = mid - 1; }
+        const int i = __ldg(prm.order + lo);
+        const int sp = __ldg(prm.split + i);
+        const int width = 32 / sp;
+        const int rel = task - __ldg(prm.start + lo);
+        const int chain = (rel / sp) * 32 + (rel % sp) * width + lane;
+        bool live = lane < width && chain < st.n_chains;
         const size_t sidx = (size_t)i * st.nch_pad + (live ? chain : 0);
         const size_t mc = (size_t)(live ? chain : 0) * V + i;
         C.cnt_row = st.counts + mc * V;
@@ -1038,17 +1046,65 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
     }
 }
 
-// vertices by cost, most expensive first (ties by index): order[rank] = vertex
-__global__ void order_kernel(const unsigned long long* __restrict__ cost, int V, int* __restrict__ order) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= V) return;
-    const unsigned long long ci = cost[i];
-    int rank = 0;
-    for (int j = 0; j < V; ++j) {
-        const unsigned long long cj = cost[j];
-        rank += (cj > ci || (cj == ci && j < i)) ? 1 : 0;
+// ------------------------------------------------------------------------------------------------
+// Task schedule of one launch.  A task = (vertex, slab of 32 chains, part): the 32 chains of a slab
+// are run by `split` warps, 32 / split lanes each.  A vertex whose micro-chains sit in the BIG tier
+// costs a warp one cooperative pass per such lane and step; spreading its slab over more warps
+// shortens its tasks so that the persistent grid still drains evenly (longest tasks first).
+//   cost[v]        warp cycles of all tasks of v in the previous launch (split_prev[v] parts per slab)
+//   order[rank]    vertex, by estimated cycles per task, descending
+//   start[rank]    first task id of that vertex; start[V] = number of tasks
+// One CTA; V is at most a few thousand.
+// ------------------------------------------------------------------------------------------------
+__global__ void schedule_kernel(const unsigned long long* __restrict__ cost, int V, int n_slabs, int n_warps, int have_cycles,
+                                int* __restrict__ split /* in: previous, out: this launch */, int* __restrict__ order,
+                                int* __restrict__ start, double* __restrict__ est /* V, scratch */) {
+    __shared__ double sh_min, sh_sum;
+    __shared__ unsigned long long sh_bits;
+    if (threadIdx.x == 0) { sh_sum = 0.0; sh_bits = 0x7ff0000000000000ull; }
+    __syncthreads();
+    // mean cycles per task of each vertex in the previous launch
+    double lsum = 0.0;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+        const double c = (double)cost[v];
+        const double t = c / ((double)n_slabs * (double)split[v]);
+        est[v] = t;
+        lsum += c;
+        if (t > 0.0) atomicMin(&sh_bits, (unsigned long long)__double_as_longlong(t));    // positive doubles order like their bit patterns
     }
-    order[rank] = i;
+    atomicAdd(&sh_sum, lsum);
+    __syncthreads();
+    if (threadIdx.x == 0) sh_min = __longlong_as_double((long long)sh_bits);
+    __syncthreads();
+    const double base = sh_min;                                // a task with no BIG lanes
+    const double target = 0.4 * sh_sum / (double)n_warps;      // no task longer than this share of a warp's load
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+        int sp = 1;
+        double e = est[v];
+        if (have_cycles && base < 1e300) {
+            const double big = fmax(e - base, 0.0) * (double)split[v];      // the part that shrinks with the split
+            e = base + big;
+            while (sp < 8 && e > target) { sp *= 2; e = base + big / (double)sp; }
+        }
+        split[v] = sp;
+        est[v] = e;
+    }
+    __syncthreads();
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+        const double ev = est[v];
+        int rank = 0;
+        for (int j = 0; j < V; ++j) {
+            const double ej = est[j];
+            rank += (ej > ev || (ej == ev && j < v)) ? 1 : 0;
+        }
+        order[rank] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int r = 0; r < V; ++r) { start[r] = acc; acc += n_slabs * split[order[r]]; }
+        start[V] = acc;
+    }
 }
 
 // first launch: no measured cost yet; estimate from the state, sum over chains of (k+1)^2
