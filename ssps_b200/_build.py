@@ -11,7 +11,7 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(_HERE, "libssps_b200.so")
+LIB_PATH = os.environ.get("SSPS_LIB") or os.path.join(_HERE, "libssps_b200.so")   # SSPS_LIB: experiment builds
 SOURCES = [os.path.join(CSRC, "ssps_capi.cu")]
 DEPS = SOURCES + [os.path.join(CSRC, "ssps_kernels.cuh"), os.path.join(CSRC, "ssps_mh.cuh"),
                   os.path.join(os.path.dirname(_HERE), "include", "ssps.h")]
@@ -38,7 +38,8 @@ def is_stale() -> bool:
 
 def build(force: bool = False, verbose: bool = False) -> str:
     if force or is_stale():
-        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + SOURCES
+        extra = os.environ.get("SSPS_NVCC_EXTRA", "").split()       # experiments: -DSSPS_KS=5 -DSSPS_MIN_CTAS=4 ...
+        cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + SOURCES
         subprocess.check_call(cmd)
     return LIB_PATH
 
