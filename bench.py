@@ -95,8 +95,8 @@ def run_reference(args, rank, world):
     cores = os.cpu_count() or 1
     chains = cores
     # size one step for ~3 s of CPU work
-    t, nprop, _ = P.run_chains_mt(chains, cores, 20, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
-    sweeps = max(20, int(20 * 3.0 / max(t, 1e-3)))
+    t, nprop, _ = P.run_chains_mt(chains, cores, 2000, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    sweeps = max(2000, int(2000 * 3.0 / max(t, 1e-3)))
     for w in range(args.warmup):
         P.run_chains_mt(chains, cores, sweeps, seed=2 + w, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
     tot_t, tot_p = 0.0, 0
@@ -115,8 +115,17 @@ def run_reference(args, rank, world):
                    "chains": chains, "sweeps_per_step": sweeps},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "time_to_psrf": None if args.no_psrf else time_to_psrf_cpu(args),
         "note": "reference runtime (Julia 1.6 + Gen 0.4.5) unavailable on this box; CPU port of its algorithm, an upper bound on its speed",
     }))
+
+
+def _cpu_rate_sample(P, orc, cores, target_s):
+    """Run the reference-faithful oracle on all cores for about target_s seconds; returns (seconds, proposals, sweeps)."""
+    t, nprop, _ = P.run_chains_mt(cores, cores, 2000, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    sweeps = max(2000, int(2000 * target_s / max(t, 1e-3)))
+    t, nprop, _ = P.run_chains_mt(cores, cores, sweeps, seed=3, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    return t, nprop, sweeps
 
 
 def cpu_baseline(args):
@@ -124,12 +133,107 @@ def cpu_baseline(args):
     ds, xm, xp = make_workload(args.V, args.T, args.M)
     P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std)
     cores = os.cpu_count() or 1
-    t, nprop, _ = P.run_chains_mt(cores, cores, 20, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
-    sweeps = max(20, int(20 * 12.0 / max(t, 1e-3)))
-    t, nprop, _ = P.run_chains_mt(cores, cores, sweeps, seed=3, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    t, nprop, sweeps = _cpu_rate_sample(P, orc, cores, 12.0)
     return {"value": nprop / t, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": "%d chains x %d sweeps (%.1f s) of the same workload, oracle QR scorer + [i;S] lml cache, one chain per thread"
                       % (cores, sweeps, t)}
+
+
+def _split_psrf_max(counts, N):
+    """max edge split-PSRF from per-chain cumulative tallies (compute_psrf_neff, postprocess_samples.jl:99-138; quirk Q6):
+    counts = {n: array [chain, V*V]} at n = N/2, 3N/4, N (burn-in 0.5)."""
+    b, sp = N // 2, N // 2 + (N - N // 2) // 2
+    n1, n2 = sp - b, N - sp
+    m1 = (counts[sp] - counts[b]) / n1
+    m2 = (counts[N] - counts[sp]) / n2
+    means = np.concatenate([m1, m2], axis=0)
+    var = np.concatenate([m1 * (1 - m1) * n1 / (n1 - 1), m2 * (1 - m2) * n2 / (n2 - 1)], axis=0)
+    n = n1
+    W = var.mean(axis=0)
+    B = n * ((means - means.mean(axis=0)) ** 2).mean(axis=0)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        psrf = np.sqrt(((n - 1) * W / n + B / n) / W)
+    ok = np.isfinite(psrf) & (W > 0)
+    return float(psrf[ok].max()) if ok.any() else float("nan")
+
+
+def time_to_psrf_cpu(args):
+    """M2 on the host: wall time until the max edge split-PSRF (burn-in 0.5) of `cores` oracle chains drops below the
+    threshold, checked every `psrf_check` sweeps; bounded by --psrf-max-seconds."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import oracle as orc
+    ds, xm, xp = make_workload(args.V, args.T, args.M)
+    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std)
+    cores = os.cpu_count() or 1
+    chains = []
+    for c in range(cores):
+        ch = orc.Chain(P, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE)
+        ch.init(args.seed, c)
+        ch.recorder_enable()
+        chains.append(ch)
+    g = args.psrf_check // 4
+    snaps, done, psrf, reached = {}, 0, float("nan"), False
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(cores) as pool:
+        while done < args.psrf_max_sweeps and time.perf_counter() - t0 < args.psrf_max_seconds:
+            list(pool.map(lambda ch: ch.run(g), chains))          # ctypes releases the GIL: one chain per core
+            done += g
+            snaps[done] = np.stack([ch.edge_counts().reshape(-1) for ch in chains]).astype(np.float64)
+            if done % args.psrf_check == 0:
+                psrf = _split_psrf_max(snaps, done)
+                for n in [n for n in snaps if n < done // 2]:
+                    del snaps[n]
+                if psrf < args.psrf_threshold:
+                    reached = True
+                    break
+    return {"threshold": args.psrf_threshold, "reached": reached, "seconds": time.perf_counter() - t0, "sweeps": done,
+            "chains": cores, "max_edge_psrf": psrf, "check_every": args.psrf_check,
+            "what": "oracle (QR scorer + lml cache), one chain per core, tallies snapshotted every %d sweeps" % g}
+
+
+def time_to_psrf_gpu(args, rank, world, local_rank, stream, dev):
+    """M2 on the device: wall time (host clock, everything included: set_data, init, sweeps, PSRF reductions) until the max
+    edge split-PSRF over ALL ranks' chains drops below the threshold, checked every `psrf_check` sweeps."""
+    import torch
+    import torch.distributed as dist
+    from ssps_b200 import Sampler
+    ds, xm, xp = make_workload(args.V, args.T, args.M)
+    C = args.psrf_chains
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    smp = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=args.psrf_check // 4)
+    smp.set_stream(stream.cuda_stream)
+    smp.set_data(xm, xp, ds.prior_graph)
+    smp.generate(C, seed=args.seed + 17, chain_id_offset=rank * C)
+    sums = torch.zeros(smp.psrf_sums_len(), dtype=torch.float64, device=dev)
+    done, psrf, reached = 0, float("nan"), False
+    stop = torch.zeros(1, dtype=torch.int32, device=dev)
+    while done < args.psrf_max_sweeps:
+        smp.update_loop(args.psrf_check)
+        done += args.psrf_check
+        smp.psrf_sums_device(0.5, sums.data_ptr())
+        if world > 1:
+            dist.all_reduce(sums)
+        psrf = smp.psrf_finish(None, device_ptr=sums.data_ptr())[0]
+        reached = psrf < args.psrf_threshold
+        over = time.perf_counter() - t0 > args.psrf_max_seconds
+        stop[0] = 1 if (reached or over) else 0
+        if world > 1:
+            dist.all_reduce(stop, op=dist.ReduceOp.MAX)      # every rank leaves the loop at the same check
+        if int(stop.item()):
+            break
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    smp.close()
+    tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    return {"threshold": args.psrf_threshold, "reached": bool(reached), "seconds": float(tt.item()), "sweeps": done,
+            "chains": C * world, "max_edge_psrf": psrf, "check_every": args.psrf_check,
+            "what": "%d chains per GPU (one resident warp per 32 micro-chains, so every chain advances concurrently); "
+                    "wall clock incl. set_data, init and the PSRF reductions" % C}
 
 
 def run_ours(args, rank, world, local_rank):
@@ -245,6 +349,7 @@ def run_ours(args, rank, world, local_rank):
                "what": "per step: ssps_create + set_data(H2D) + init_chains + %d sweeps + psrf + edge_posterior(D2H), wall clock" % S}
 
     smp.close()
+    ttp = None if args.no_psrf else time_to_psrf_gpu(args, rank, world, local_rank, stream, dev)
     if rank != 0:
         return
     out = {
@@ -258,6 +363,7 @@ def run_ours(args, rank, world, local_rank):
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(st1.kernel_launches - st0.kernel_launches),
         "clocks": clk.summary(), "max_edge_psrf": max_psrf,
         "accept_rate": float(agg[1].item()) / max(proposals, 1.0),
+        "time_to_psrf": ttp,
     }
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args)
@@ -280,6 +386,12 @@ def main():
     ap.add_argument("--lambda-prop-std", type=float, default=3.0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-psrf", action="store_true", help="skip the wall-time-to-PSRF<threshold measurement (metric M2)")
+    ap.add_argument("--psrf-chains", type=int, default=512, help="chains per GPU for M2")
+    ap.add_argument("--psrf-threshold", type=float, default=1.1)
+    ap.add_argument("--psrf-check", type=int, default=1000, help="sweeps between convergence checks (multiple of 4)")
+    ap.add_argument("--psrf-max-sweeps", type=int, default=400000)
+    ap.add_argument("--psrf-max-seconds", type=float, default=60.0)
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))

@@ -515,7 +515,8 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     occ = std::max(1, occ);
     const int n_tasks = V * (h->nch_pad / 32);
     const int warps_per_cta = SSPS_BLOCK / 32;
-    h->mh_grid = std::max(1, std::min(h->sm_count * occ, div_up((size_t)n_tasks, warps_per_cta)));
+    // room for the scheduler to spread a slab over up to SSPS_MAX_SPLIT warps
+    h->mh_grid = std::max(1, std::min(h->sm_count * occ, div_up((size_t)n_tasks * SSPS_MAX_SPLIT, warps_per_cta)));
     const size_t nthreads = (size_t)h->mh_grid * SSPS_BLOCK;
     const size_t kc = (size_t)h->kcap;
     CK(h->big_d.alloc(nthreads * SSPS_ROWLEN(kc)));
@@ -526,7 +527,7 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     CK(h->x_t.alloc(nthreads * 2 * kc));
     CK(h->task_counter.alloc(1));
     CK(h->order.alloc(V)); CK(h->vcost.alloc(V));
-    CK(h->task_start.alloc((size_t)V + 1)); CK(h->task_split.alloc(V)); CK(h->task_est.alloc(V));
+    CK(h->task_start.alloc((size_t)V + 1)); CK(h->task_split.alloc(V)); CK(h->task_est.alloc(2 * (size_t)V));
     {
         std::vector<int> ones((size_t)V, 1);
         CK(cudaMemcpyAsync(h->task_split.p, ones.data(), sizeof(int) * (size_t)V, cudaMemcpyHostToDevice, s));
@@ -1134,7 +1135,7 @@ int ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len) {
     return SSPS_OK;
 }
 
-int ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles, int32_t* mean_indeg_x1000) {
+int ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles, int32_t* mean_indeg_x1000, int32_t* split) {
     CKS(bind(h));
     if (h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "no chains");
     const int V = h->V;
@@ -1144,6 +1145,7 @@ int ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles, int32_t* mean_indeg_x1
         CK(cudaMemcpy(c.data(), h->vcost.p, sizeof(unsigned long long) * V, cudaMemcpyDeviceToHost));
         for (int i = 0; i < V; ++i) cycles[i] = (int64_t)c[i];
     }
+    if (split) CK(cudaMemcpy(split, h->task_split.p, sizeof(int) * V, cudaMemcpyDeviceToHost));
     if (mean_indeg_x1000) {
         std::vector<int> k((size_t)V * h->nch_pad);
         CK(cudaMemcpy(k.data(), h->k.p, sizeof(int) * k.size(), cudaMemcpyDeviceToHost));

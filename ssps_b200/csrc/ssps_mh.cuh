@@ -1050,47 +1050,81 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
 // Task schedule of one launch.  A task = (vertex, slab of 32 chains, part): the 32 chains of a slab
 // are run by `split` warps, 32 / split lanes each.  A vertex whose micro-chains sit in the BIG tier
 // costs a warp one cooperative pass per such lane and step; spreading its slab over more warps
-// shortens its tasks so that the persistent grid still drains evenly (longest tasks first).
+// shortens its tasks, so that the persistent grid drains evenly (longest tasks first) and, when
+// there are fewer tasks than resident warps, so that a sweep takes as long as ONE cooperative pass.
 //   cost[v]        warp cycles of all tasks of v in the previous launch (split_prev[v] parts per slab)
 //   order[rank]    vertex, by estimated cycles per task, descending
 //   start[rank]    first task id of that vertex; start[V] = number of tasks
-// One CTA; V is at most a few thousand.
+// Model: a task of v at split s costs  base + big_v / s  (base = a task without BIG lanes); the launch
+// takes about  all task cycles / resident warps + SSPS_TAIL_WEIGHT x longest task  (list scheduling, longest
+// first: the bound has weight 1, a full grid hides most of the tail: 0.1 measured best).  Greedy: keep halving the lanes of the
+// longest task while that lowers this estimate.  One CTA; V is at most a few thousand.
 // ------------------------------------------------------------------------------------------------
-__global__ void schedule_kernel(const unsigned long long* __restrict__ cost, int V, int n_slabs, int n_warps, int have_cycles,
-                                int* __restrict__ split /* in: previous, out: this launch */, int* __restrict__ order,
-                                int* __restrict__ start, double* __restrict__ est /* V, scratch */) {
-    __shared__ double sh_min, sh_sum;
+#define SSPS_MAX_SPLIT 32
+#ifndef SSPS_TAIL_WEIGHT
+#define SSPS_TAIL_WEIGHT 0.1
+#endif
+__global__ void __launch_bounds__(256) schedule_kernel(const unsigned long long* __restrict__ cost, int V, int n_slabs, int n_warps,
+                                                       int have_cycles, int* __restrict__ split /* in: previous, out: this launch */,
+                                                       int* __restrict__ order, int* __restrict__ start,
+                                                       double* __restrict__ est /* 2 V scratch: task estimate, big part */) {
+    __shared__ double sh_sum, sh_val[8];
+    __shared__ int sh_idx[8], sh_stop;
     __shared__ unsigned long long sh_bits;
-    if (threadIdx.x == 0) { sh_sum = 0.0; sh_bits = 0x7ff0000000000000ull; }
+    double* __restrict__ big = est + V;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) { sh_sum = 0.0; sh_bits = 0x7ff0000000000000ull; sh_stop = 0; }
     __syncthreads();
     // mean cycles per task of each vertex in the previous launch
-    double lsum = 0.0;
-    for (int v = threadIdx.x; v < V; v += blockDim.x) {
-        const double c = (double)cost[v];
-        const double t = c / ((double)n_slabs * (double)split[v]);
+    for (int v = tid; v < V; v += blockDim.x) {
+        const double t = (double)cost[v] / ((double)n_slabs * (double)split[v]);
         est[v] = t;
-        lsum += c;
         if (t > 0.0) atomicMin(&sh_bits, (unsigned long long)__double_as_longlong(t));    // positive doubles order like their bit patterns
+    }
+    __syncthreads();
+    const double base = __longlong_as_double((long long)sh_bits);
+    const bool model = have_cycles && base < 1e300;
+    double lsum = 0.0;
+    for (int v = tid; v < V; v += blockDim.x) {
+        const double bg = model ? fmax(est[v] - base, 0.0) * (double)split[v] : 0.0;
+        big[v] = bg;
+        if (model) est[v] = base + bg;          // at split 1
+        split[v] = 1;
+        lsum += est[v];
     }
     atomicAdd(&sh_sum, lsum);
     __syncthreads();
-    if (threadIdx.x == 0) sh_min = __longlong_as_double((long long)sh_bits);
-    __syncthreads();
-    const double base = sh_min;                                // a task with no BIG lanes
-    const double target = 0.4 * sh_sum / (double)n_warps;      // no task longer than this share of a warp's load
-    for (int v = threadIdx.x; v < V; v += blockDim.x) {
-        int sp = 1;
-        double e = est[v];
-        if (have_cycles && base < 1e300) {
-            const double big = fmax(e - base, 0.0) * (double)split[v];      // the part that shrinks with the split
-            e = base + big;
-            while (sp < 8 && e > target) { sp *= 2; e = base + big / (double)sp; }
+    if (model) {
+        double load = sh_sum * (double)n_slabs / (double)n_warps;      // all task cycles / resident warps
+        for (int it = 0; it < 5 * V; ++it) {
+            // longest task
+            double bv = -1.0; int bi = -1;
+            for (int v = tid; v < V; v += blockDim.x) { const double e = est[v]; if (e > bv) { bv = e; bi = v; } }
+            for (int o = 16; o > 0; o >>= 1) {
+                const double ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bv || (ov == bv && oi >= 0 && (bi < 0 || oi < bi))) { bv = ov; bi = oi; }
+            }
+            if (lane == 0) { sh_val[wid] = bv; sh_idx[wid] = bi; }
+            __syncthreads();
+            if (tid == 0) {
+                for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
+                    if (sh_val[w] > bv || (sh_val[w] == bv && sh_idx[w] >= 0 && (bi < 0 || sh_idx[w] < bi))) { bv = sh_val[w]; bi = sh_idx[w]; }
+                const int sp = split[bi];
+                const double cur = SSPS_TAIL_WEIGHT * bv + load;
+                const double e_new = base + big[bi] / (double)(2 * sp);
+                const double load_new = load + (double)n_slabs * (double)sp * base / (double)n_warps;   // sp more tasks, each + base
+                // the runner-up is not known here; e_new bounds the new longest task from below, which is enough to reject
+                if (sp >= SSPS_MAX_SPLIT || big[bi] <= 0.0 || SSPS_TAIL_WEIGHT * e_new + load_new >= cur) sh_stop = 1;
+                else { split[bi] = 2 * sp; est[bi] = e_new; sh_sum = load_new; }
+            }
+            __syncthreads();
+            if (sh_stop) break;
+            load = sh_sum;
+            __syncthreads();
         }
-        split[v] = sp;
-        est[v] = e;
     }
     __syncthreads();
-    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+    for (int v = tid; v < V; v += blockDim.x) {
         const double ev = est[v];
         int rank = 0;
         for (int j = 0; j < V; ++j) {
@@ -1100,7 +1134,7 @@ __global__ void schedule_kernel(const unsigned long long* __restrict__ cost, int
         order[rank] = v;
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
         int acc = 0;
         for (int r = 0; r < V; ++r) { start[r] = acc; acc += n_slabs * split[order[r]]; }
         start[V] = acc;

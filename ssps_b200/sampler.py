@@ -293,11 +293,12 @@ class Sampler:
         return h
 
     def vertex_cost(self):
-        """(warp cycles per vertex in the last MH launch, mean in-degree per vertex now)."""
+        """(warp cycles per vertex in the last MH launch, mean in-degree per vertex now, warps per slab in that launch)."""
         c = np.zeros(self.V, dtype=np.int64)
         k = np.zeros(self.V, dtype=np.int32)
-        check(self._L.ssps_get_vertex_cost(self._h, _l(c), k.ctypes.data_as(C.POINTER(C.c_int32))))
-        return c, k / 1000.0
+        sp = np.zeros(self.V, dtype=np.int32)
+        check(self._L.ssps_get_vertex_cost(self._h, _l(c), k.ctypes.data_as(C.POINTER(C.c_int32)), sp.ctypes.data_as(C.POINTER(C.c_int32))))
+        return c, k / 1000.0, sp
 
     def measure_fp64_peak(self) -> float:
         t = C.c_double(0.0)

@@ -27,12 +27,13 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
         print("      big: %.0f cycles per big lane-step, %.3f of all task cycles" % ((st.big_cycles - prev.big_cycles) / max(st.n_big_steps - prev.n_big_steps, 1),
               (st.big_cycles - prev.big_cycles) / max(float(s.vertex_cost()[0].sum()) * 4, 1.0)))
         prev = st
-    cost, mk = s.vertex_cost()
+    cost, mk, sp = s.vertex_cost()
     n_slabs = (C + 31) // 32
-    o = np.argsort(-cost)
-    print("kernel ms last rep / launches:", dms, "grid warps:", "?")
-    print("per-task mean cycles by vertex (top 12):", [(int(i), round(cost[i] / n_slabs / 1e6, 3), round(float(mk[i]), 2)) for i in o[:12]])
-    print("sum task Mcycles %.1f, max task Mcycles %.3f, median %.3f" % (cost.sum() / 1e6, cost.max() / n_slabs / 1e6, np.median(cost) / n_slabs / 1e6))
+    task = cost / (n_slabs * sp)
+    o = np.argsort(-task)
+    print("kernel ms last rep:", dms)
+    print("(vertex, Mcycles per task, split, mean indeg) top 12:", [(int(i), round(task[i] / 1e6, 3), int(sp[i]), round(float(mk[i]), 2)) for i in o[:12]])
+    print("sum task Mcycles %.1f, tasks %d, max task Mcycles %.3f, median %.3f, split hist %s" % (cost.sum() / 1e6, int((n_slabs * sp).sum()), task.max() / 1e6, np.median(task) / 1e6, np.bincount(sp).tolist()))
     print("mean indeg hist:", np.histogram(mk, bins=[0, 1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 16, 32, 64])[0])
     if os.environ.get('DIAG_KHIST'):
         print("khist:", s.khist(40).tolist())
