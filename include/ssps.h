@@ -194,6 +194,8 @@ int  ssps_changepoints_get(ssps_handle* h, int32_t chain,
 
 int  ssps_get_stats(ssps_handle* h, ssps_run_stats* out);
 int  ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len);
+/* The MH kernel's raw counter block (csrc/ssps_mh.cuh, enum ST_*), for profiling builds. */
+int  ssps_get_raw_stats(ssps_handle* h, int64_t* out, int32_t len);
 /* Diagnostics of the task scheduler: per vertex, the warp cycles its tasks cost in the last MH launch, 1000 x the
  * mean in-degree over the local chains now, and the number of warps its slabs were spread over (any may be NULL). */
 int  ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles /* V */, int32_t* mean_indeg_x1000 /* V */, int32_t* split /* V */);

@@ -71,6 +71,7 @@ SIGNATURES = {
     "ssps_changepoints_get": (C.c_int, [_hp, C.c_int32, _lp, _ip, _ip, _ip, _lp, _ip, _dp]),
     "ssps_get_stats": (C.c_int, [_hp, C.POINTER(RunStats)]),
     "ssps_get_khist": (C.c_int, [_hp, _lp, C.c_int32]),
+    "ssps_get_raw_stats": (C.c_int, [_hp, _lp, C.c_int32]),
     "ssps_get_vertex_cost": (C.c_int, [_hp, _lp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "ssps_measure_fp64_peak": (C.c_int, [_hp, _dp]),
 }

@@ -1124,6 +1124,16 @@ int ssps_get_stats(ssps_handle* h, ssps_run_stats* out) {
     return SSPS_OK;
 }
 
+int ssps_get_raw_stats(ssps_handle* h, int64_t* out, int32_t len) {
+    CKS(bind(h));
+    if (!out || len < 1 || h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "bad buffer or no chains");
+    unsigned long long st[ST_N];
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(st, h->stats.p, sizeof st, cudaMemcpyDeviceToHost));
+    for (int a = 0; a < len; ++a) out[a] = a < ST_N ? (int64_t)st[a] : 0;
+    return SSPS_OK;
+}
+
 int ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len) {
     CKS(bind(h));
     if (!hist || len < 1) return fail(SSPS_ERR_INVALID, "bad buffer");

@@ -54,7 +54,9 @@ struct SspsDev {
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                               uint32_t k0, uint32_t k1, uint32_t out[4]) {
-#pragma unroll
+    // rolled on purpose: the MH kernel is bound by instruction fetch, not issue (profiles/): 140 fewer static
+    // instructions per call site measured +2.5 % proposals/s
+#pragma unroll 1
     for (int r = 0; r < 10; ++r) {
         uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
         uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;

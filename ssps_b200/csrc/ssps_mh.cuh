@@ -50,7 +50,7 @@
 enum { MODE_SMALL = 0, MODE_BIG = 1, MODE_PROMOTE = 2 };
 // stats slots (unsigned long long each)
 enum { ST_ACCP = 0, ST_ACCL = 1, ST_SUMK = 2, ST_F3 = 3, ST_BYTES = 4, ST_OVERFLOW = 5, ST_PROP = 6, ST_TIER1 = 7,
-       ST_MISMATCH = 10, ST_BIG_CYCLES = 11, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_N = 16 };
+       ST_MISMATCH = 10, ST_BIG_CYCLES = 11, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_PROF = 16, ST_N = 32 };
 
 __device__ __forceinline__ float fast_lg2(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float fast_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -563,23 +563,35 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
 //
 // The warp copies the lane's state into its Stage, applies the move to the copy IN PLACE
 // (ids_remove / fac_remove, then fac_append / ids_append) and reads off q of the proposed set; the
-// copy goes back to the arena only if the move is accepted.
+// copy goes back to the arena (or to the lane's SMALL slots) only if the move is accepted.
 //
 // The rows after a removal are refactorised RIGHT-LOOKING: once column b is final, every lane
 // subtracts its product from the entries (a, c), c > b, it owns.  Each entry therefore receives
 // the terms of  G_ac - sum_m l_am l_cm  in ascending m through fma -- the operation order of the
 // row-by-row factorisation in orc_lml_chol -- so the result is the same bit pattern.
 // ------------------------------------------------------------------------------------------------
+// The factor in the Stage stays in the coordinates it was loaded in.  A removal of arrival slot p only
+// marks row p and column p DEAD (pd = p; pd = SSPS_NODEAD when nothing was removed): position a of the
+// proposed set lives in stage row / column a + (a >= pd).  Nothing is moved until the copy leaves the
+// Stage (stage_store / stage_to_small compact it on the way out).  The id list IS compacted at once.
+#define SSPS_NODEAD (1 << 20)
+__device__ __forceinline__ int st_map(const int a, const int pd) { return a + (a >= pd ? 1 : 0); }
+
 __device__ __forceinline__ void stage_load(const Stage T, const BigRef B, const int k, const int lane) {
     for (int e = lane; e < SSPS_TRI(k); e += 32) T.t[e] = B.f[e];
     const double* __restrict__ fw = B.fw();
     for (int a = lane; a < k; a += 32) { T.tw[a] = fw[a]; T.id[a] = B.w[a]; T.rk[a] = B.r[a]; }
     __syncwarp();
 }
-__device__ __forceinline__ void stage_store(const Stage T, const BigRef B, const int k, const int lane) {
-    for (int e = lane; e < SSPS_TRI(k); e += 32) B.f[e] = T.t[e];
+// kn rows of the proposed set -> the lane's arena block
+__device__ __forceinline__ void stage_store(const Stage T, const BigRef B, const int kn, const int pd, const int lane) {
+    for (int a = 0; a < kn; ++a) {
+        const double* __restrict__ row = T.t + SSPS_TRI(st_map(a, pd));
+        double* __restrict__ dst = B.f + SSPS_TRI(a);
+        for (int m = lane; m <= a; m += 32) dst[m] = row[st_map(m, pd)];
+    }
     double* __restrict__ fw = B.fw();
-    for (int a = lane; a < k; a += 32) { fw[a] = T.tw[a]; B.w[a] = T.id[a]; B.r[a] = T.rk[a]; }
+    for (int a = lane; a < kn; a += 32) { fw[a] = T.tw[st_map(a, pd)]; B.w[a] = T.id[a]; B.r[a] = T.rk[a]; }
     __syncwarp();
 }
 // SMALL-tier slots of one lane <-> Stage
@@ -588,9 +600,12 @@ __device__ __forceinline__ void stage_from_small(const Stage T, const SmallAcc S
     if (lane < k) { T.tw[lane] = Ss.Wv(lane); T.id[lane] = Ss.W(lane); T.rk[lane] = (uint16_t)Ss.rank(lane); }
     __syncwarp();
 }
-__device__ __forceinline__ void stage_to_small(const Stage T, const SmallAcc Ss, const int k, const int lane) {
-    for (int e = lane; e < SSPS_TRI(k); e += 32) Ss.d[e * SSPS_BLOCK] = T.t[e];
-    if (lane < k) { Ss.Wv(lane) = T.tw[lane]; Ss.W(lane) = T.id[lane]; Ss.set_rank(lane, (int)T.rk[lane]); }
+__device__ __forceinline__ void stage_to_small(const Stage T, const SmallAcc Ss, const int kn, const int pd, const int lane) {
+    for (int a = 0; a < kn; ++a) {
+        const double* __restrict__ row = T.t + SSPS_TRI(st_map(a, pd));
+        if (lane <= a) Ss.d[(SSPS_TRI(a) + lane) * SSPS_BLOCK] = row[st_map(lane, pd)];
+    }
+    if (lane < kn) { Ss.Wv(lane) = T.tw[st_map(lane, pd)]; Ss.W(lane) = T.id[lane]; Ss.set_rank(lane, (int)T.rk[lane]); }
     __syncwarp();
 }
 
@@ -624,94 +639,115 @@ __device__ __forceinline__ void ids_append(const Stage T, const int kr, const in
     __syncwarp();
 }
 
-// Factor after the removal of arrival slot p of k (T.id already holds the reduced list, the rows are
-// still in the old coordinates).  q_in = sum of w_m^2 over m < p; returns q over all k - 1 rows.
+// pair number idx -> (u, v), 0 <= u <= v, idx = v (v + 1) / 2 + u: the pairs of a triangle with n rows are idx < n (n + 1) / 2
+__device__ __forceinline__ void tri_decode(const int idx, int& u, int& v) {
+    int vv = (int)((sqrtf((float)(8 * idx + 1)) - 1.0f) * 0.5f);
+    while (vv * (vv + 1) / 2 > idx) --vv;
+    while ((vv + 1) * (vv + 2) / 2 <= idx) ++vv;
+    v = vv; u = idx - vv * (vv + 1) / 2;
+}
+
+// Factor after the removal of arrival slot p of k: rows p .. k-2 of the reduced set (stage rows p+1 .. k-1;
+// T.id already holds the reduced list).  q_in = sum of w_m^2 over m < p; returns q over all k - 1 rows.
+// The trailing triangle is spread over the lanes pair by pair (a, c), c <= a, numbered from the LAST row
+// upwards, so that the pairs still alive at step b are always a prefix of the lane's list.
 __device__ __noinline__ double fac_remove(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int k, const int p,
                                           double q, const int lane) {
-    const int V = P.V, kr = k - 1;
+    const int V = P.V, kr = k - 1, nt = kr - p;
     double* t = T.t; double* tw = T.tw;
-    if (p >= kr) return q;
-    // rows a >= p keep the entries m < p of old row a + 1 (lane m carries column m through all rows: no cross-lane hazard)
-    for (int a = p; a < kr; ++a)
-        for (int m = lane; m < p; m += 32) t[SSPS_TRI(a) + m] = t[SSPS_TRI(a + 1) + m];
-    __syncwarp();
-    // partial sums over the unchanged columns m < p; pseudo-column a + 1 = t_a
-    for (int a = p; a < kr; ++a) {
+    if (nt <= 0) return q;
+#define SROW(a) (t + SSPS_TRI((a) + 1))      /* a >= p: stage row a + 1 */
+#define SCOL(c) ((c) + 1)                    /* c >= p: stage column c + 1 */
+    // partial sums over the unchanged columns m < p; the diagonal pair of row a also carries t_a
+    for (int idx = lane; idx < nt * (nt + 1) / 2; idx += 32) {
+        int u, v;
+        tri_decode(idx, u, v);
+        const int a = kr - 1 - u, c = kr - 1 - v;
         const int ja = T.idof(a);
-        const double* __restrict__ Ga = P.G + (size_t)ja * V;
-        double* ra = t + SSPS_TRI(a);
-        for (int c = p + lane; c <= a + 1; c += 32) {
-            if (c <= a) {
-                double x = __ldg(Ga + T.idof(c));
-                const double* rc = t + SSPS_TRI(c);
-                for (int m = 0; m < p; ++m) x = fma(-ra[m], rc[m], x);
-                ra[c] = x;
-            } else {
-                double x = __ldg(Ri + ja);
-                for (int m = 0; m < p; ++m) x = fma(-ra[m], tw[m], x);
-                tw[a] = x;
-            }
+        double* ra = SROW(a);
+        const double* rc = SROW(c);
+        double x = __ldg(P.G + (size_t)ja * V + T.idof(c));
+        if (c == a) {
+            double xt = __ldg(Ri + ja);
+            for (int m = 0; m < p; ++m) { const double l = ra[m]; x = fma(-l, l, x); xt = fma(-l, tw[m], xt); }
+            tw[a + 1] = xt;
+        } else {
+            for (int m = 0; m < p; ++m) x = fma(-ra[m], rc[m], x);
         }
+        ra[SCOL(c)] = x;
     }
     __syncwarp();
     for (int b = p; b < kr; ++b) {
         const int jb = T.idof(b);
         const double gbb = __ldg(P.G + (size_t)jb * V + jb);
-        const double d2 = t[SSPS_TRI(b) + b], tb = tw[b];
+        double* rb = SROW(b);
+        const double d2 = rb[SCOL(b)], tb = tw[b + 1];
         double inv, wb;
         chol_pivot(d2, gbb, tb, inv, wb, q);
         __syncwarp();                               // every lane has read d2 and t_b
-        if (lane == 0) { t[SSPS_TRI(b) + b] = inv; tw[b] = wb; }
-        for (int a = b + 1 + lane; a < kr; a += 32) {     // column b and its share of t_a
-            const double l = t[SSPS_TRI(a) + b] * inv;
-            t[SSPS_TRI(a) + b] = l;
-            tw[a] = fma(-l, wb, tw[a]);
+        if (lane == 0) { rb[SCOL(b)] = inv; tw[b + 1] = wb; }
+        const int nr = kr - 1 - b;                  // rows below b
+        for (int idx = lane; idx < nr * (nr + 1) / 2; idx += 32) {
+            int u, v;
+            tri_decode(idx, u, v);
+            const int a = kr - 1 - u, c = kr - 1 - v;
+            double* ra = SROW(a);
+            const double lab = ra[SCOL(b)] * inv;
+            if (c == a) {
+                ra[SCOL(a)] = fma(-lab, lab, ra[SCOL(a)]);
+                tw[a + 1] = fma(-lab, wb, tw[a + 1]);
+            } else {
+                const double lcb = SROW(c)[SCOL(b)] * inv;
+                ra[SCOL(c)] = fma(-lab, lcb, ra[SCOL(c)]);
+            }
         }
-        __syncwarp();
-        for (int a = b + 1; a < kr; ++a) {                // trailing entries (a, c), b < c <= a
-            const double lab = t[SSPS_TRI(a) + b];
-            for (int c = b + 1 + lane; c <= a; c += 32) t[SSPS_TRI(a) + c] = fma(-lab, t[SSPS_TRI(c) + b], t[SSPS_TRI(a) + c]);
-        }
-        __syncwarp();
+        __syncwarp();                               // column b has been read by everyone: scale it in place
+        for (int a = b + 1 + lane; a < kr; a += 32) { double* ra = SROW(a); ra[SCOL(b)] = ra[SCOL(b)] * inv; }
     }
+    __syncwarp();
+#undef SROW
+#undef SCOL
     return q;
 }
 
-// Row kr of the factor: parent j appended to the kr rows in the Stage (forward substitution, lane owns
-// columns lane + 32 u).  Returns q + w_kr^2.
-__device__ __noinline__ double fac_append(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int kr, const int j,
-                                          double q, const int lane) {
+// Row kr of the proposed set's factor: parent j appended to its kr rows (forward substitution, lane owns
+// columns lane + 32 u).  pd = dead stage row / column (SSPS_NODEAD: none).  Returns q + w_kr^2.
+__device__ __noinline__ double fac_append(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int kr, const int pd,
+                                          const int j, double q, const int lane) {
     const int V = P.V;
     double* t = T.t; double* tw = T.tw;
     const double* __restrict__ Gj = P.G + (size_t)j * V;
     const double gjj = __ldg(Gj + j);
     double d2 = gjj, tj = __ldg(Ri + j);
     double sc[SSPS_KU];
+    const double* myrow[SSPS_KU];
 #pragma unroll
     for (int u = 0; u < SSPS_KU; ++u) {
         const int c = lane + 32 * u;
         sc[u] = (c < kr) ? __ldg(Gj + T.idof(c)) : 0.0;
+        myrow[u] = t + SSPS_TRI(st_map(c < kr ? c : 0, pd));
     }
-    double* rj = t + SSPS_TRI(kr);
+    double* rj = t + SSPS_TRI(st_map(kr, pd));
     for (int b = 0; b < kr; ++b) {
-        const double invb = t[SSPS_TRI(b) + b];
-        const double wb = tw[b];
+        const int sb = st_map(b, pd);
+        const double invb = t[SSPS_TRI(sb) + sb];
+        const double wb = tw[sb];
         double mine = sc[0];
 #pragma unroll
         for (int u = 1; u < SSPS_KU; ++u) if ((b >> 5) == u) mine = sc[u];
         const double l = __shfl_sync(SSPS_FULL, mine * invb, b & 31);
         d2 = fma(-l, l, d2);
         tj = fma(-l, wb, tj);
-        if (lane == (b & 31)) rj[b] = l;
+        if (lane == (b & 31)) rj[sb] = l;
 #pragma unroll
         for (int u = 0; u < SSPS_KU; ++u) {
             const int c = lane + 32 * u;
-            if (c > b && c < kr) sc[u] = fma(-l, t[SSPS_TRI(c) + b], sc[u]);
+            if (c > b && c < kr) sc[u] = fma(-l, myrow[u][sb], sc[u]);
         }
     }
     double inv, wj;
     chol_pivot(d2, gjj, tj, inv, wj, q);
-    if (lane == 0) { rj[kr] = inv; tw[kr] = wj; }
+    if (lane == 0) { rj[st_map(kr, pd)] = inv; tw[st_map(kr, pd)] = wj; }
     __syncwarp();
     return q;
 }
@@ -730,6 +766,9 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
     const double* __restrict__ Ri = P.R + (size_t)V * child;
     unsigned n_big = 0, n_t1 = 0;
     const long long t_in = clock64();
+#ifdef SSPS_PROFILE_BIG
+    long long prof_[8] = {0, 0, 0, 0, 0, 0, 0, 0}; long long tp_ = clock64();
+#endif
     while (bigm) {
         const int src = __ffs(bigm) - 1;
         bigm &= bigm - 1;
@@ -747,8 +786,16 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
             if (lane == src) { atomicExch(C.stats + ST_OVERFLOW, 1ull); *acc_kn = kn << 1; }
             continue;
         }
+
+#ifdef SSPS_PROFILE_BIG
+        { const long long tn_ = clock64(); prof_[0] += tn_ - tp_; tp_ = tn_; }
+#endif
         const Stage T = C.stage(k + 1);
         stage_load(T, B, k, lane);
+#ifdef SSPS_PROFILE_BIG
+        { const long long tn_ = clock64(); prof_[1] += tn_ - tp_; tp_ = tn_; }
+#endif
+
         int j_add = -1, j_rem = -1, p = k;
         uint32_t w_rem = 0;
         if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
@@ -768,6 +815,10 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
             w_rem = T.id[p];
             j_rem = (int)(w_rem & 0xffffu);
         }
+
+#ifdef SSPS_PROFILE_BIG
+        { const long long tn_ = clock64(); prof_[2] += tn_ - tp_; tp_ = tn_; }
+#endif
         // ---- apply the move to the working copy ----
         double q_new = 0.0;
         {
@@ -775,15 +826,24 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
             for (int m = 0; m < pm; ++m) { const double wm = T.tw[m]; q_new = fma(wm, wm, q_new); }
         }
         int kr = k;
+        const int pd = has_rem ? p : SSPS_NODEAD;
         if (has_rem) {
             ids_remove(T, k, p, lane);
             q_new = fac_remove(P, Ri, T, k, p, q_new, lane);
             kr = k - 1;
         }
+
+#ifdef SSPS_PROFILE_BIG
+        { const long long tn_ = clock64(); prof_[3] += tn_ - tp_; tp_ = tn_; }
+#endif
         if (has_add) {
-            q_new = fac_append(P, Ri, T, kr, j_add, q_new, lane);
+            q_new = fac_append(P, Ri, T, kr, pd, j_add, q_new, lane);
             ids_append(T, kr, j_add, rel_now, lane);
         }
+
+#ifdef SSPS_PROFILE_BIG
+        { const long long tn_ = clock64(); prof_[4] += tn_ - tp_; tp_ = tn_; }
+#endif
         int acc = 0;
         if (lane == src) {
             double fwd, bwd;
@@ -816,23 +876,33 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
             }
             *acc_kn = acc | (kn << 1);
         }
+
+#ifdef SSPS_PROFILE_BIG
+        { const long long tn_ = clock64(); prof_[5] += tn_ - tp_; tp_ = tn_; }
+#endif
         acc = __shfl_sync(SSPS_FULL, acc, src);
         if (acc) {
-            if (kn <= SSPS_KS) stage_to_small(T, S.of_lane(src - lane), kn, lane);
-            else stage_store(T, B, kn, lane);
+            if (kn <= SSPS_KS) stage_to_small(T, S.of_lane(src - lane), kn, pd, lane);
+            else stage_store(T, B, kn, pd, lane);
         }
     }
+#ifdef SSPS_PROFILE_BIG
+    { const long long tn_ = clock64(); prof_[6] += tn_ - tp_; tp_ = tn_; }
+#endif
     while (pend) {          // arrivals accepted by small_move with |S'| = SSPS_KS + 1
         const int src = __ffs(pend) - 1;
         pend &= pend - 1;
         const int j_add = __shfl_sync(SSPS_FULL, L.pend_j, src);
         const Stage T = C.stage(SSPS_KS + 1);
         stage_from_small(T, S.of_lane(src - lane), SSPS_KS, lane);
-        fac_append(P, Ri, T, SSPS_KS, j_add, 0.0, lane);
+        fac_append(P, Ri, T, SSPS_KS, SSPS_NODEAD, j_add, 0.0, lane);
         ids_append(T, SSPS_KS, j_add, rel_now, lane);
-        stage_store(T, C.big(src), SSPS_KS + 1, lane);
+        stage_store(T, C.big(src), SSPS_KS + 1, SSPS_NODEAD, lane);
         if (lane == src) { L.mode = MODE_BIG; L.k = SSPS_KS + 1; }
     }
+#ifdef SSPS_PROFILE_BIG
+    if (lane == 0) { prof_[7] += clock64() - tp_; for (int e_ = 0; e_ < 8; ++e_) atomicAdd(C.stats + ST_PROF + e_, (unsigned long long)prof_[e_]); }
+#endif
     if (lane == 0) {
         if (n_big) atomicAdd(C.stats + ST_BIG_STEPS, (unsigned long long)n_big);
         atomicAdd(C.stats + ST_BIG_CYCLES, (unsigned long long)(clock64() - t_in));
@@ -859,8 +929,8 @@ __device__ __noinline__ Lane task_settle(const SspsDev& P, const int child, Lane
         for (int a = lane; a < k; a += 32) { T.id[a] = B.w[a]; T.rk[a] = B.r[a]; }
         __syncwarp();
         double q = 0.0;
-        for (int a = 0; a < k; ++a) q = fac_append(P, Ri, T, a, T.idof(a), q, lane);
-        stage_store(T, B, k, lane);
+        for (int a = 0; a < k; ++a) q = fac_append(P, Ri, T, a, SSPS_NODEAD, T.idof(a), q, lane);
+        stage_store(T, B, k, SSPS_NODEAD, lane);
         if (lane == src) lane_set_q(P, child, L, q);
     }
     return L;

@@ -292,6 +292,11 @@ class Sampler:
         check(self._L.ssps_get_khist(self._h, _l(h), length))
         return h
 
+    def raw_stats(self, length: int = 32) -> np.ndarray:
+        h = np.zeros(length, dtype=np.int64)
+        check(self._L.ssps_get_raw_stats(self._h, _l(h), length))
+        return h
+
     def vertex_cost(self):
         """(warp cycles per vertex in the last MH launch, mean in-degree per vertex now, warps per slab in that launch)."""
         c = np.zeros(self.V, dtype=np.int64)

@@ -37,3 +37,9 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
     print("mean indeg hist:", np.histogram(mk, bins=[0, 1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 16, 32, 64])[0])
     if os.environ.get('DIAG_KHIST'):
         print("khist:", s.khist(40).tolist())
+    if os.environ.get('DIAG_PROF'):
+        r = s.raw_stats(32)
+        names = ["select+bcast", "stage_load", "scans", "remove (+q prefix)", "append", "accept (src lane)", "commit", "promote+tail"]
+        tot = float(r[16:24].sum()) or 1.0
+        print("BIG phase cycles by section (profiling build): " + ", ".join("%s %.1f%%" % (n, 100 * r[16 + e] / tot) for e, n in enumerate(names)),
+              "| per big lane-step %.0f" % (tot / max(st.n_big_steps, 1)))
