@@ -7,7 +7,7 @@
  *
  *   ssps_set_data / ssps_set_timeseries
  *        combine_X / standardize_X / vectorize_X        SSPS/src/dbn_preprocess.jl:70-108
- *        compute_B_col / construct_B (regression_deg 1) SSPS/src/dbn_distributions.jl:168-194
+ *        compute_B_col / construct_B                    SSPS/src/dbn_distributions.jl:168-194
  *        prob_param_i, lambda_min                       SSPS/src/SSPS.jl:164-169
  *   ssps_score
  *        log_marg_lik / compute_lml / safe_solve        SSPS/src/dbn_distributions.jl:201-264
@@ -57,7 +57,7 @@ typedef enum {
     SSPS_OK = 0,
     SSPS_ERR_INVALID = -1,      /* bad argument / call order */
     SSPS_ERR_CUDA = -2,         /* CUDA runtime error (message has the cudaError string) */
-    SSPS_ERR_UNSUPPORTED = -3,  /* e.g. regression_deg != 1, --proposal uniform */
+    SSPS_ERR_UNSUPPORTED = -3,  /* e.g. a set too large for the interaction-column path, --proposal uniform */
     SSPS_ERR_NOMEM = -4,
     SSPS_ERR_INDEGREE = -5,     /* a proposed parent set exceeded max_indegree scratch */
     SSPS_ERR_UNAVAILABLE = -6   /* e.g. PSRF requested before any snapshot exists */
@@ -68,7 +68,10 @@ typedef struct ssps_handle ssps_handle;
 typedef struct {
     int32_t struct_size;      /* = sizeof(ssps_config) */
     int32_t device;           /* CUDA ordinal; -1 = current device */
-    int32_t regression_deg;   /* --regression-deg; only 1 is implemented */
+    int32_t regression_deg;   /* --regression-deg (SSPS.jl:75-78).  1: the tabulated-Gram path.  >= 2: interaction columns
+                                 (construct_B), every proposal scored from scratch, sets limited to 12 parents / 48
+                                 design columns.  <= 0 (the reference CLI's default -1): the reference builds an EMPTY
+                                 design -- flat likelihood -- reproduced as is (quirk Q2) */
     int32_t max_indegree;     /* scratch capacity for |S'| (0 = min(V, 64)); sets may still hold up to V parents
                                  only if <= this bound */
     double  large_indeg;      /* --large-indeg   (SSPS.jl:64-67)  */

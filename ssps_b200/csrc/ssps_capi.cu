@@ -13,6 +13,7 @@
 #include "../../include/ssps.h"
 #include "ssps_kernels.cuh"
 #include "ssps_mh.cuh"
+#include "ssps_poly.cuh"
 
 #include <algorithm>
 #include <chrono>
@@ -104,6 +105,10 @@ struct ssps_handle {
     DevBuf<float> lam_margin;
     double lambda_min = 0.0;
     SspsDev dev{};
+    PolyDev poly{};                 // regression_deg != 1: interaction-column path (csrc/ssps_poly.cuh)
+    bool is_poly = false;
+    DevBuf<double> poly_arena;
+    int poly_grid = 0;
 
     // ---- chains (K3) ----
     int n_chains = 0, nch_pad = 0;
@@ -267,6 +272,7 @@ int finish_data(ssps_handle* h, const double* prior_host) {
     d.grp_off = h->grp_off.p; d.grp_omc = h->grp_omc.p; d.grp_mult = h->grp_mult.p;
     d.mvP = h->mvP.p; d.mvLogP = h->mvLogP.p; d.logint = h->logint.p;
     d.fgrp_off = h->fgrp_off.p; d.fgrp = h->fgrp.p; d.lam_margin = h->lam_margin.p;
+    h->poly.Xminus = h->Xminus.p; h->poly.Y = h->Y.p; h->poly.deg = h->cfg.regression_deg;
     h->has_data = true;
     // any chains belong to the previous data set
     h->n_chains = 0;
@@ -294,9 +300,6 @@ int ssps_create(const ssps_config* cfg, ssps_handle** out) {
     if (!cfg || !out) return fail(SSPS_ERR_INVALID, "ssps_create: null argument");
     if (cfg->struct_size != (int32_t)sizeof(ssps_config))
         return fail(SSPS_ERR_INVALID, "ssps_config.struct_size=%d, library expects %d", cfg->struct_size, (int)sizeof(ssps_config));
-    if (cfg->regression_deg != 1)
-        return fail(SSPS_ERR_UNSUPPORTED, "regression_deg=%d: only the degree-1 design is implemented (DESIGN.md, out of scope)",
-                    cfg->regression_deg);
     if (!(cfg->large_indeg > 0.0) || !(cfg->lambda_prop_std > 0.0))
         return fail(SSPS_ERR_INVALID, "large_indeg and lambda_prop_std must be positive");
     int ndev = 0;
@@ -308,6 +311,7 @@ int ssps_create(const ssps_config* cfg, ssps_handle** out) {
     ssps_handle* h = new (std::nothrow) ssps_handle();
     if (!h) return fail(SSPS_ERR_NOMEM, "out of host memory");
     h->cfg = *cfg;
+    h->is_poly = cfg->regression_deg != 1;
     h->device = dev;
     cudaError_t e = cudaSetDevice(dev);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, dev);
@@ -436,6 +440,27 @@ int ssps_score(ssps_handle* h, int32_t n_sets, const int32_t* child, const int32
     const int kcap = std::max(kmax, 1);
     const int block = 128, grid = div_up((size_t)n_sets, block);
     const size_t nthreads = (size_t)grid * block;
+    if (h->is_poly) {       // interaction columns: every set from scratch (csrc/ssps_poly.cuh)
+        if (h->cfg.regression_deg > 0 && (kmax > SSPS_POLY_KMAX || poly_width(kmax, h->cfg.regression_deg) < 0))
+            return fail(SSPS_ERR_UNSUPPORTED, "regression_deg=%d: a set of %d parents needs more than %d design columns (or %d parents)",
+                        h->cfg.regression_deg, kmax, SSPS_POLY_MMAX, SSPS_POLY_KMAX);
+        DevBuf<int> d_child, d_off, d_mem;
+        DevBuf<double> d_lam, d_lml, d_lp, arena;
+        CKS(upload(h, d_child, child, (size_t)n_sets));
+        CKS(upload(h, d_off, set_offsets, (size_t)n_sets + 1));
+        CKS(upload(h, d_mem, set_members, (size_t)total));
+        if (lambda) CKS(upload(h, d_lam, lambda, (size_t)n_sets));
+        CK(d_lml.alloc(n_sets)); CK(d_lp.alloc(n_sets));
+        CK(arena.alloc(nthreads * (size_t)SSPS_POLY_SCRATCH_DOUBLES));
+        poly_score_kernel<<<grid, block, 0, h->stream>>>(h->dev, h->poly, n_sets, d_child.p, d_off.p, d_mem.p, lambda ? d_lam.p : nullptr,
+                                                         arena.p, d_lml.p, logprior_out ? d_lp.p : nullptr);
+        CKS(launch_ok(h, "poly_score_kernel"));
+        if (lml_out) CKS(download(h, lml_out, d_lml.p, (size_t)n_sets));
+        if (logprior_out) CKS(download(h, logprior_out, d_lp.p, (size_t)n_sets));
+        CK(cudaStreamSynchronize(h->stream));
+        if (min_pivot_out) for (int e = 0; e < n_sets; ++e) min_pivot_out[e] = std::nan("");
+        return SSPS_OK;
+    }
     DevBuf<int> d_child, d_off, d_mem;
     DevBuf<double> d_lam, d_lml, d_lp, d_minp, arena_d;
     DevBuf<uint16_t> arena_t;
@@ -538,6 +563,14 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     CK(cudaMemsetAsync(h->khist.p, 0, h->khist.bytes(), s));
     CK(cudaMemsetAsync(h->vcost.p, 0, h->vcost.bytes(), s));
     h->have_cost = false;
+
+    if (h->is_poly) {
+        int occ_p = 1;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_p, (const void*)mh_poly_kernel<PhiloxSource>, 128, 0));
+        h->poly_grid = std::max(1, std::min(h->sm_count * std::max(1, occ_p), div_up((size_t)n_tasks, 4)));
+        CK(h->poly_arena.alloc((size_t)h->poly_grid * 128 * SSPS_POLY_SCRATCH_DOUBLES));
+        h->kcap = std::min(h->kcap, SSPS_POLY_KMAX);
+    }
 
     h->thinning = 0; h->sweeps_done = 0; h->samples_recorded = 0;
     h->kernel_ms = 0.0; h->mh_launches = 0;
@@ -748,7 +781,15 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
             h->ev_pool.emplace_back(a, b);
         }
         CK(cudaEventRecord(h->ev_pool[ev_used].first, h->stream));
-        if (replay_host) {
+        if (h->is_poly) {
+            if (replay_host) {
+                ReplaySource src{replay_dev.p + (size_t)done * C * V * 6, C, V};
+                mh_poly_kernel<ReplaySource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p);
+            } else {
+                PhiloxSource src{h->seed, h->chain_offset};
+                mh_poly_kernel<PhiloxSource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p);
+            }
+        } else if (replay_host) {
             ReplaySource src{replay_dev.p + (size_t)done * C * V * 6, C, V};
             if (h->cfg.verify) mh_sweeps_kernel<ReplaySource, true><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
             else mh_sweeps_kernel<ReplaySource, false><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
@@ -874,6 +915,15 @@ int ssps_get_state(ssps_handle* h, int32_t chain, int32_t* indeg, int32_t* membe
         int64_t o = 0;
         for (int i = 0; i < V; ++i)
             for (int a = 0; a < kk[i]; ++a) members[o++] = mem[(size_t)i * V + a];
+    }
+    if (lml && h->is_poly) {
+        std::vector<int32_t> ch(V), off(V + 1, 0), mm;
+        for (int i = 0; i < V; ++i) {
+            ch[i] = i; off[i + 1] = off[i] + kk[i];
+            for (int a = 0; a < kk[i]; ++a) mm.push_back(mem[(size_t)i * V + a]);
+        }
+        if (mm.empty()) mm.push_back(0);
+        return ssps_score(h, V, ch.data(), off.data(), mm.data(), nullptr, lml, nullptr, nullptr);
     }
     if (lml) {
         const int block = 128, grid = div_up((size_t)V, block);

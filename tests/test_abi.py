@@ -54,9 +54,9 @@ def test_create_validates_config():
     assert L.ssps_create(ctypes.byref(cfg), ctypes.byref(h)) == _lib.ERR_INVALID
     assert b"struct_size" in L.ssps_last_error()
     cfg.struct_size = ctypes.sizeof(_lib.Config)
-    cfg.regression_deg = 2
-    cfg.large_indeg, cfg.lambda_max, cfg.lambda_prop_std = 20.0, 15.0, 0.25
-    assert L.ssps_create(ctypes.byref(cfg), ctypes.byref(h)) == _lib.ERR_UNSUPPORTED
+    cfg.regression_deg = 1
+    cfg.large_indeg, cfg.lambda_max, cfg.lambda_prop_std = -1.0, 15.0, 0.25
+    assert L.ssps_create(ctypes.byref(cfg), ctypes.byref(h)) == _lib.ERR_INVALID
     assert L.ssps_create(None, None) == _lib.ERR_INVALID
 
 

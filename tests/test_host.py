@@ -75,8 +75,6 @@ def test_recover_state():
 def test_unsupported_modes_exit_loudly():
     from ssps_b200.ssps_wrapper import perform_inference
     with pytest.raises(SystemExit):
-        perform_inference("a", "b", "c", 1.0, 10, 1, 20.0, 15.0, -1, 0.25, "sparse", "", False)
-    with pytest.raises(SystemExit):
         perform_inference("a", "b", "c", 1.0, 10, 1, 20.0, 15.0, 1, 0.25, "uniform", "", False)
 
 
