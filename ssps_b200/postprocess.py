@@ -59,3 +59,169 @@ def write_genie(path, probs_child_major, node_names):
         f.write("node1,node2,score\n")
         for a, b, s in genie_edge_list(probs_child_major, node_names):
             f.write("%s,%s,%r\n" % (a, b, s))
+
+
+# ---------------------------------------------------------------------------------------------------
+# Twin of scripts/postprocess_samples.jl for per-chain sample files (the reference's or ours):
+#     python -m ssps_b200.postprocess --chain-samples c1.json c2.json ... --output-file out.json
+#                                     [--stop-points n1 n2 ...] [--burnin 0.5]
+# Restates load_samples (:23-35), ChangepointVec (changepoint_vec.jl), compute_psrf_neff (:99-138),
+# correlation_sum (:58-91), evaluate_convergence (:155-180), evaluate_summary (:183-191),
+# collect_stats (:212-233) and postprocess_sample_files (:242-259), on dense sequences.
+# ---------------------------------------------------------------------------------------------------
+import numpy as _np
+
+
+def load_samples(path: str) -> dict:
+    """load_samples: parent_sets[i] becomes a list over ALL V parents (missing key -> no change points)."""
+    import json
+    with open(path) as f:
+        d = json.load(f)
+    V = len(d["parent_sets"])
+    d["parent_sets"] = [[ps.get(str(p), []) for p in range(1, V + 1)] for ps in d["parent_sets"]]
+    return d
+
+
+def dense_sequence(changepoints, n: int) -> _np.ndarray:
+    """ChangepointVec(changepoints, n) as a dense vector over positions 1..n: the value at t is that of the
+    last change point with index <= t (index 0 = the initial state), default 0 (changepoint_vec.jl getindex)."""
+    out = _np.zeros(n, dtype=_np.float64)
+    for a, (t, v) in enumerate(changepoints):
+        t_next = changepoints[a + 1][0] if a + 1 < len(changepoints) else n + 1
+        lo, hi = max(int(t), 1), min(int(t_next) - 1, n)
+        if hi >= lo:
+            out[lo - 1:hi] = v
+    return out
+
+
+def _is_binary(changepoints) -> bool:
+    return all(v == 0 or v == 1 for _, v in changepoints)
+
+
+def correlation_sum(seqs, varplus: float, is_binary: bool) -> float:
+    """correlation_sum (:58-91) incl. its accumulation rule: at lag t > 2 the correlation of lag t - 2 is
+    added while corr(t) + corr(t - 1) >= 0.  seqs: list of 1-D arrays (lags run to len(seqs[0]) - 2; every
+    sequence's variogram uses its own length, as seq_variogram does)."""
+    m = len(seqs)
+    s, prev2, prev1 = 0.0, 0.0, 0.0
+    for t in range(1, len(seqs[0]) - 1):
+        comb = 0.0
+        for q in seqs:
+            nq = len(q)
+            if is_binary:
+                comb += float((q[:nq - t] != q[t:]).sum()) / (nq - t)
+            else:
+                dq = q[:nq - t] - q[t:]
+                comb += float((dq * dq).sum()) / (nq - t)
+        comb /= m
+        with _np.errstate(divide="ignore", invalid="ignore"):
+            corr = float(1.0 - _np.float64(comb) / _np.float64(2.0 * varplus))
+        if t > 2:
+            if corr + prev1 >= 0.0:
+                s += prev2
+            else:
+                break
+        prev2, prev1 = prev1, corr
+    return s
+
+
+def compute_psrf_neff(half_seqs, is_binary: bool):
+    """compute_psrf_neff (:99-138): half_seqs = list of 1-D arrays (m half-chains); n = len(half_seqs[0]);
+    B uses 1/m (quirk Q6)."""
+    m, n = len(half_seqs), len(half_seqs[0])
+    means, variances = _np.zeros(m), _np.zeros(m)
+    for a, q in enumerate(half_seqs):
+        N = len(q)
+        if is_binary:
+            means[a] = float((q != 0).sum()) / N
+            variances[a] = means[a] * (1.0 - means[a]) * N / (N - 1)
+        else:
+            means[a] = float(q.sum()) / N
+            variances[a] = float(((q - means[a]) ** 2).sum()) / (N - 1)
+    B = n * float(((means - means.sum() / m) ** 2).sum()) / m
+    W = float(variances.sum()) / m
+    vp = (n - 1) * W / n + B / n
+    with _np.errstate(divide="ignore", invalid="ignore"):
+        psrf = float(_np.sqrt(_np.float64(vp) / _np.float64(W)))
+    corr_sum = correlation_sum(half_seqs, vp, is_binary)
+    n_eff = m * n / (1.0 + 2.0 * corr_sum)
+    return psrf, n_eff
+
+
+def evaluate_convergence(whole_seqs, ns, stop_points, burnin=0.5, is_binary=None):
+    """evaluate_convergence (:155-180): whole_seqs = change-point lists of ONE quantity, one per chain."""
+    if is_binary is None:
+        is_binary = _is_binary(whole_seqs[0])
+    dense = [dense_sequence(cp, n) for cp, n in zip(whole_seqs, ns)]
+    out = []
+    for ln in stop_points:
+        b = int(math.floor(burnin * ln))
+        sp = b + (ln - b) // 2
+        halves = []
+        for d in dense:
+            halves.append(d[b:sp]); halves.append(d[sp:ln])
+        out.append(compute_psrf_neff(halves, is_binary))
+    return out
+
+
+def evaluate_summary(whole_seqs, ns, burnin=0.5) -> float:
+    """evaluate_summary (:183-191): pooled mean after each chain's own burn-in (stop points are ignored there too)."""
+    tot, cnt = 0.0, 0
+    for cp, n in zip(whole_seqs, ns):
+        b = int(math.floor(burnin * n))
+        d = dense_sequence(cp, n)
+        tot += float(d[b:].sum()); cnt += n - b
+    return tot / cnt
+
+
+def collect_stats(dict_vec, stop_points, burnin=0.5) -> dict:
+    """collect_stats (:212-233): same tree as the reference's output JSON."""
+    V = len(dict_vec[0]["parent_sets"])
+    ns = [int(d["n"]) for d in dict_vec]
+
+    def conv(seqs):
+        return [[_num(p), _num(e)] for p, e in evaluate_convergence(seqs, ns, stop_points, burnin)]
+
+    ps_sum = [[evaluate_summary([d["parent_sets"][i][j] for d in dict_vec], ns, burnin) for j in range(V)] for i in range(V)]
+    ps_conv = [[conv([d["parent_sets"][i][j] for d in dict_vec]) for j in range(V)] for i in range(V)]
+    lam_sum = [evaluate_summary([d["lambda"][i] for d in dict_vec], ns, burnin) for i in range(len(dict_vec[0]["lambda"]))]
+    lam_conv = [conv([d["lambda"][i] for d in dict_vec]) for i in range(len(dict_vec[0]["lambda"]))]
+    return {
+        "stop_points": list(stop_points),
+        "summary": {"lambda": lam_sum},
+        "conv_stats": {"parent_sets": ps_conv, "lambda": lam_conv},
+        "parent_sets": ps_sum,
+        "edge_conf_key": "parent_sets",
+        "t_elapsed": [d["t_elapsed"] for d in dict_vec],
+        "n": ns,
+    }
+
+
+def postprocess_sample_files(sample_filenames, output_file, stop_points=(), burnin=0.5) -> dict:
+    """postprocess_sample_files (:242-259)."""
+    import json
+    dict_vec = [load_samples(f) for f in sample_filenames]
+    n_max = min(int(d["n"]) for d in dict_vec)
+    stop_points = [n_max] if len(stop_points) == 0 else [sp for sp in stop_points if sp <= n_max]
+    results = collect_stats(dict_vec, stop_points, burnin)
+    with open(output_file, "w") as f:
+        json.dump(results, f)
+    print("Saved postprocessed MCMC results to", output_file)
+    return results
+
+
+def main(argv=None) -> int:
+    import argparse
+    ap = argparse.ArgumentParser(prog="postprocess_samples")
+    ap.add_argument("--chain-samples", nargs="+", required=True, help="mcmc sample files for one or more chains")
+    ap.add_argument("--stop-points", nargs="+", type=int, default=[], help="points in the sequence where convergence should be analyzed.")
+    ap.add_argument("--burnin", type=float, default=0.5, help="fraction of sequence to discard as burnin.")
+    ap.add_argument("--output-file", required=True, help="name of output JSON file containing convergence information")
+    a = ap.parse_args(argv)
+    postprocess_sample_files(a.chain_samples, a.output_file, a.stop_points, a.burnin)
+    return 0
+
+
+if __name__ == "__main__":
+    import sys
+    sys.exit(main())
