@@ -4,7 +4,7 @@ Levels (BASELINE.json north_star / SURVEY 8c):
   L1  lml / logprior for fixed parent sets: <= 1e-10 relative vs the reference-faithful QR oracle;
   L2  replayed random stream: accept/reject decisions and parent sets bit-exact vs the
       kernel-faithful (Gram-Cholesky) oracle;
-  L3  edge posteriors within Monte-Carlo error (test_gpu_posterior.py).
+  L3  edge posteriors within Monte-Carlo error (tests/test_gpu_configs.py, config C2).
 """
 import numpy as np
 import pytest
