@@ -232,7 +232,7 @@ def time_to_psrf_gpu(args, rank, world, local_rank, stream, dev):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     return {"threshold": args.psrf_threshold, "reached": bool(reached), "seconds": float(tt.item()), "sweeps": done,
             "chains": C * world, "max_edge_psrf": psrf, "check_every": args.psrf_check,
-            "what": "%d chains per GPU (one resident warp per 32 micro-chains, so every chain advances concurrently); "
+            "what": "%d chains per GPU (few chains: the scheduler gives heavy micro-chains a warp of their own, so a sweep costs one step latency); "
                     "wall clock incl. set_data, init and the PSRF reductions" % C}
 
 
@@ -305,14 +305,28 @@ def run_ours(args, rank, world, local_rank):
     gbytes = st1.algorithmic_bytes - st0.algorithmic_bytes
     nprop_local = st1.n_proposals - st0.n_proposals
     ach = flops / (k_ms * 1e-3) / 1e12
-    roofline = {"bound": "fp64", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": None,
+    # numbers of the committed `ncu --set full` capture of this kernel (tools/ncu_traffic.py), quoted only for the launch shape it was taken on
+    ncu, traffic = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "mh_sweeps_ncu.json")) as f:
+            ncu = json.load(f)
+        if (V, C, S // 4) == (100, 4096, 100):
+            traffic = ncu["dram_bytes_per_launch"]
+    except Exception:
+        ncu = None
+    roofline = {"bound": "fp64", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": traffic,
                 "kernel": "mh_sweeps_kernel<PhiloxSource>", "launches": launches, "avg_launch_ms": k_ms / max(launches, 1),
                 "kernel_share_of_step": k_ms / ms,
                 "peak_source": "DFMA peak measured on this GPU by ssps_measure_fp64_peak (MEASURED_PEAKS.json has no FP64 figure)",
                 "mean_k": (st1.sum_k - st0.sum_k) / max(nprop_local, 1),
                 "algorithmic_flops_per_proposal": flops / max(nprop_local, 1),
                 "gather_GBps": gbytes / (k_ms * 1e-3) / 1e9,
-                "kernel_proposals_per_s": nprop_local / (k_ms * 1e-3)}
+                "kernel_proposals_per_s": nprop_local / (k_ms * 1e-3),
+                "note": "the FP64 fraction is small by construction (33 flops per proposal); the kernel is bound by instruction "
+                        "fetch/issue latency: see issue_slot_utilisation_pct and stall_cycles_per_issue (ncu, profiles/)",
+                "ncu": None if ncu is None else {k: ncu[k] for k in ("source", "launch", "issue_slot_utilisation_pct", "fp64_pipe_active_pct",
+                                                                    "warp_instructions_per_launch", "stall_cycles_per_issue",
+                                                                    "l1_hit_pct", "l2_hit_pct", "registers_per_thread")}}
 
     # ---- e2e: host buffers in, posterior out, every step ----
     e2e = None
@@ -387,12 +401,14 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-psrf", action="store_true", help="skip the wall-time-to-PSRF<threshold measurement (metric M2)")
-    ap.add_argument("--psrf-chains", type=int, default=512, help="chains per GPU for M2")
+    ap.add_argument("--psrf-chains", type=int, default=128, help="chains per GPU for M2 (few: every micro-chain gets its own warp)")
     ap.add_argument("--psrf-threshold", type=float, default=1.1)
-    ap.add_argument("--psrf-check", type=int, default=1000, help="sweeps between convergence checks (multiple of 4)")
-    ap.add_argument("--psrf-max-sweeps", type=int, default=400000)
-    ap.add_argument("--psrf-max-seconds", type=float, default=60.0)
+    ap.add_argument("--psrf-check", type=int, default=4000, help="sweeps between convergence checks (multiple of 4)")
+    ap.add_argument("--psrf-max-sweeps", type=int, default=3000000)
+    ap.add_argument("--psrf-max-seconds", type=float, default=None, help="default: 90 s on the GPU arm, 240 s on the CPU arm")
     args = ap.parse_args()
+    if args.psrf_max_seconds is None:
+        args.psrf_max_seconds = 240.0 if args.impl == "reference" else 90.0
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -403,7 +419,9 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl")
+        import torch
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
         run_ours(args, rank, world, local_rank)
     finally:
