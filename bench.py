@@ -133,7 +133,7 @@ def cpu_baseline(args):
     ds, xm, xp = make_workload(args.V, args.T, args.M)
     P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std)
     cores = os.cpu_count() or 1
-    t, nprop, sweeps = _cpu_rate_sample(P, orc, cores, 12.0)
+    t, nprop, sweeps = _cpu_rate_sample(P, orc, cores, 20.0)
     return {"value": nprop / t, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": "%d chains x %d sweeps (%.1f s) of the same workload, oracle QR scorer + [i;S] lml cache, one chain per thread"
                       % (cores, sweeps, t)}
