@@ -538,6 +538,7 @@ int alloc_chains(ssps_handle* h, int n_chains) {
         for (const void* f : fns) CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
     }
     occ = std::max(1, occ);
+    if (const char* e = getenv("SSPS_MAX_OCC")) occ = std::max(1, std::min(occ, atoi(e)));      // experiments: resident CTAs per SM
     const int n_tasks = V * (h->nch_pad / 32);
     const int warps_per_cta = SSPS_BLOCK / 32;
     // room for the scheduler to spread a slab over up to SSPS_MAX_SPLIT warps

@@ -39,18 +39,24 @@
 #ifndef SSPS_KS
 #define SSPS_KS 6
 #endif
+#ifndef SSPS_LOCKSTEP
+#define SSPS_LOCKSTEP 1      // 1: the warps of a scheduler walk the sweep in step (named barrier per sweep); 2: the whole CTA; 0: off
+#endif
+#ifndef SSPS_LS_EVERY
+#define SSPS_LS_EVERY 1      // sweeps between the lock-step barriers (power of two)
+#endif
 #ifndef SSPS_BLOCK
-#define SSPS_BLOCK 128
+#define SSPS_BLOCK 384       // one CTA per SM: three warps per scheduler
 #endif
 #ifndef SSPS_MIN_CTAS
-#define SSPS_MIN_CTAS 3
+#define SSPS_MIN_CTAS 1
 #endif
 #define SSPS_LN2 0.6931471805599453
 
 enum { MODE_SMALL = 0, MODE_BIG = 1, MODE_PROMOTE = 2 };
 // stats slots (unsigned long long each)
 enum { ST_ACCP = 0, ST_ACCL = 1, ST_SUMK = 2, ST_F3 = 3, ST_BYTES = 4, ST_OVERFLOW = 5, ST_PROP = 6, ST_TIER1 = 7,
-       ST_MISMATCH = 10, ST_BIG_CYCLES = 11, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_PROF = 16, ST_N = 32 };
+       ST_MISMATCH = 10, ST_BIG_CYCLES = 11, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_MID_STEPS = 14, ST_MID_CYCLES = 15, ST_PROF = 16, ST_N = 32 };
 
 __device__ __forceinline__ float fast_lg2(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float fast_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -275,8 +281,12 @@ __device__ __noinline__ int lambda_exact_decide(const SspsDev& P, const int chil
 // ------------------------------------------------------------------------------------------------
 // one Cholesky pivot (orc_lml_chol / score_set): accepted -> (1/d, t/d), q += w^2; numerically
 // dependent column -> contributes nothing; NaN data (zero-variance column, quirk Q4) -> NaN
+// 1 / sqrt(x), IEEE sqrt then IEEE division (the oracle's bits).  One out-of-line copy: inlined, the two
+// software sequences are ~45 instructions at each of the 8 pivots of the hot loop (instruction fetch)
+__device__ __noinline__ double inv_sqrt_ieee(const double x) { return 1.0 / sqrt(x); }
+
 __device__ __forceinline__ void chol_pivot(const double d2, const double gjj, const double t, double& inv, double& w, double& q) {
-    if (d2 > SSPS_PIVOT_TOL * gjj) { inv = 1.0 / sqrt(d2); w = t * inv; q = fma(w, w, q); }
+    if (d2 > SSPS_PIVOT_TOL * gjj) { inv = inv_sqrt_ieee(d2); w = t * inv; q = fma(w, w, q); }
     else if (d2 != d2 || gjj != gjj) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; q = inv; }
     else { inv = 0.0; w = 0.0; }
 }
@@ -309,6 +319,16 @@ __device__ __forceinline__ void move_ratio(const SspsDev& P, const int child, co
 
 // Gen.mh: accept iff log(u) < alpha.  Both sides are first formed with fp32 MUFU logarithms and compared
 // with a margin that bounds the screening error; closer than the margin -> the reference-order fp64 test.
+// the reference-order fp64 test (rare: out of line)
+__device__ __noinline__ int mh_accept_exact(const double log1pn, const double dn, const int action, const int k, const int kn, const double dprior,
+                                            const double fwd, const double bwd, const double ip_cur, const double ip_new, const double u_acc) {
+    const double lml_cur = -0.5 * (double)k * log1pn - 0.5 * dn * log(ip_cur);
+    const double lml_new = -0.5 * (double)kn * log1pn - 0.5 * dn * log(ip_new);
+    const double w = dprior + (lml_new - lml_cur);
+    const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
+    return log(u_acc) < alpha ? 1 : 0;
+}
+
 __device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
                                           const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
                                           const double ip_new, const float lg_new, const double u_acc, unsigned& n_t1) {
@@ -320,13 +340,24 @@ __device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, co
     bool accept = diff < 0.0;
     if (!(u_acc > 1e-30 && fabs(diff) > marg)) {        // too close (or NaN): the reference-order fp64 test
         ++n_t1;
+#ifdef SSPS_ACCEPT_OOL
+        accept = mh_accept_exact(P.log1pn, P.dn, action, k, kn, dprior, fwd, bwd, ip_cur, ip_new, u_acc) != 0;
+#else
         const double lml_cur = -0.5 * (double)k * P.log1pn - 0.5 * P.dn * log(ip_cur);
         const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
         const double w = dprior + (lml_new - lml_cur);
         const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
         accept = log(u_acc) < alpha;
+#endif
     }
     return accept;
+}
+
+// out-of-line copy for the rare tiers (mid_move, big_phase): 320 instructions per inlined instance
+__device__ __noinline__ bool mh_accept_ool(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
+                                           const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
+                                           const double ip_new, const float lg_new, const double u_acc, unsigned& n_t1) {
+    return mh_accept(P, action, k, kn, dprior, fwd, bwd, ip_cur, lg_ip_cur, ip_new, lg_new, u_acc, n_t1);
 }
 
 __device__ __forceinline__ void lane_set_q(const SspsDev& P, int child, Lane& L, double q) {
@@ -372,15 +403,18 @@ __device__ __noinline__ double small_build(const SspsDev& P, const double* __res
 // An accepted arrival that outgrows the tier leaves the lane in MODE_PROMOTE (ids and factor still
 // those of the current set, L.pend_j = the arriving parent); the warp finishes it in big_phase.
 // ------------------------------------------------------------------------------------------------
+// the step's proposal as drawn (select_move) with its proposal-ratio terms (move_ratio): formed once per step for
+// every live lane in the main loop, so that the rare tiers do not carry their own copies of that code
+struct Move { int action, a_ord, r_ord; double fwd, bwd; };
+
 #define NL(a, b) nl[SSPS_TRI(a) - (a) + (b)]       // strictly lower triangle: row a starts at a(a-1)/2
 
 template <bool VERIFY>
-__device__ __forceinline__ int small_move(const SspsDev& P, const int child, const StepDraws& d, Lane& L, const SmallAcc& S,
+__device__ __forceinline__ int small_move(const SspsDev& P, const int child, const StepDraws& d, const Move& mv, Lane& L, const SmallAcc& S,
                                           const KCtx& C, const int rel_now, const unsigned peers, unsigned& n_t1, int& kn_out) {
     constexpr int KS = SSPS_KS;
     const int V = P.V, k = L.k;
-    int action, a_ord, r_ord;
-    select_move(P, child, k, d, action, a_ord, r_ord);
+    const int action = mv.action, a_ord = mv.a_ord, r_ord = mv.r_ord;
     const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
 
     uint32_t idw[KS]; int rk[KS];
@@ -404,8 +438,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     const int kr = k - (has_rem ? 1 : 0);
     const int kn = kr + (has_add ? 1 : 0);
     kn_out = kn;
-    double fwd, bwd;
-    move_ratio(P, child, k, action, fwd, bwd);
+    const double fwd = mv.fwd, bwd = mv.bwd;
     const double* __restrict__ omc_i = P.omc + (size_t)V * child;
     const double* __restrict__ Ri = P.R + (size_t)V * child;
     double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
@@ -465,7 +498,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
                     t = fma(-l, nw[b], t);
                 }
                 if (d2 > SSPS_PIVOT_TOL * gaa) {
-                    const double invd = 1.0 / sqrt(d2);
+                    const double invd = inv_sqrt_ieee(d2);
                     ninv[a] = invd; nw[a] = t * invd;
                 } else if (d2 != d2 || gaa != gaa) {
                     ninv[a] = __longlong_as_double(0x7ff8000000000000LL); nw[a] = ninv[a];
@@ -523,8 +556,22 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
         C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
     L.somc = (L.somc - omc_rem) + omc_add;
     L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
-    if (kn > KS) {      // an arrival that outgrows shared memory (k == KS, pure add): the warp moves the lane to the BIG tier
-        L.mode = MODE_PROMOTE; L.pend_j = j_add;
+    if (kn > KS) {      // an arrival that outgrows shared memory (k == KS, pure add): the lane moves itself to the BIG tier
+        const BigRef B = C.big(threadIdx.x & 31);
+        for (int e = 0; e < SSPS_TRI(KS); ++e) B.f[e] = S.d[e * SSPS_BLOCK];
+        double* __restrict__ fw = B.fw();
+        int rj = 0;
+        for (int a = 0; a < KS; ++a) {
+            const uint32_t w = S.W(a);
+            int r = S.rank(a);
+            if ((int)(w & 0xffffu) < j_add) ++rj; else ++r;
+            B.w[a] = w; B.r[a] = (uint16_t)r; fw[a] = S.Wv(a);
+        }
+#pragma unroll
+        for (int m = 0; m < KS; ++m) B.f[SSPS_TRI(KS) + m] = jl[m];
+        B.f[SSPS_TRI(KS) + KS] = jinv; fw[KS] = jw;
+        B.w[KS] = (uint32_t)j_add | ((uint32_t)rel_now << 16); B.r[KS] = (uint16_t)rj;
+        L.mode = MODE_BIG; L.k = kn;
         return 1;
     }
     // ---- factor and id list back to shared memory ----
@@ -557,6 +604,155 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     return 1;
 }
 #undef NL
+
+// ------------------------------------------------------------------------------------------------
+// MID: the parent-set move of a BIG-tier lane whose current set has fewer than SSPS_KM members, done by
+// the lane ITSELF with rolled loops (small code, every such lane of the warp at the same time) on a
+// shared-memory copy F of its factor (a slot of the warp's Stage, filled by the whole warp: the arena
+// is global memory and a dependent chain of L2 round trips per lane cost 58 000 cycles per move).  The
+// warp-cooperative pass below costs tens of thousands of cycles whatever the size and serialises the
+// lanes; sets of 7..12 parents are 80 % of the BIG-tier proposals at the metric point and need a few
+// hundred fma.  Same rows, same operation order, same bits as small_move / big_phase.  The move is
+// applied to F in place (new row a overwrites old row a, whose only reader -- new row a - 1 -- is done);
+// the arena (ids, ranks, factor) is touched only on accept.  F: TRI-packed rows, w behind SSPS_TRI(SSPS_KM).
+// ------------------------------------------------------------------------------------------------
+#ifndef SSPS_KM
+#define SSPS_KM 16
+#endif
+#define SSPS_MID_SLOT (SSPS_ROWLEN(SSPS_KM) + SSPS_KM)            // doubles: factor, w, then ids (words) and ranks (halves)
+#define SSPS_MID_SLOTS (SSPS_ROWLEN(SSPS_KST) / SSPS_MID_SLOT)
+template <bool VERIFY>
+__device__ __noinline__ int mid_move(const SspsDev& P, const int child, const StepDraws& d, const Move& mv, Lane& L, const SmallAcc& S, const BigRef B,
+                                     double* F, const KCtx& C, const int rel_now, unsigned& n_t1, int& kn_out) {
+    const int V = P.V, k = L.k;
+    const uint32_t* Fid = (const uint32_t*)(F + SSPS_ROWLEN(SSPS_KM));      // id | rel << 16, arrival order (the CURRENT set throughout)
+    const uint16_t* Frk = (const uint16_t*)(Fid + SSPS_KM);                 // sorted ranks
+#define FID(b) ((int)(Fid[b] & 0xffffu))
+    const int action = mv.action, a_ord = mv.a_ord, r_ord = mv.r_ord;
+    const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
+    int j_add = -1, j_rem = -1, p = k, rp = 1 << 20;
+    uint32_t w_rem = 0;
+    if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
+        int c = 0;
+        #pragma unroll 1
+        for (int b = 0; b < k; ++b) c += (FID(b) - (int)Frk[b] < a_ord) ? 1 : 0;
+        j_add = a_ord - 1 + c;
+    }
+    if (has_rem) {          // the r-th element of the sorted list
+        rp = r_ord - 1;
+        #pragma unroll 1
+        for (int b = 0; b < k; ++b) if ((int)Frk[b] == rp) p = b;
+        w_rem = Fid[p]; j_rem = (int)(w_rem & 0xffffu);
+    }
+    const int kr = k - (has_rem ? 1 : 0);
+    const int kn = kr + (has_add ? 1 : 0);
+    kn_out = kn;
+    if (kn > C.kcap) { atomicExch(C.stats + ST_OVERFLOW, 1ull); return 0; }
+    const double fwd = mv.fwd, bwd = mv.bwd;
+    const double* __restrict__ omc_i = P.omc + (size_t)V * child;
+    const double* __restrict__ Ri = P.R + (size_t)V * child;
+    double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
+    if (has_add) { omc_add = __ldg(omc_i + j_add); dprior = -L.lam * omc_add; }
+    if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
+
+    double* Fw = F + SSPS_TRI(SSPS_KM);
+    double q_new = 0.0;
+    #pragma unroll 1
+    for (int m = 0; m < p && m < kr; ++m) q_new = fma(Fw[m], Fw[m], q_new);
+    // rows [p, kn) of the proposed set: old slots p + 1 .. k - 1 (entries left of column p are the cached ones), then the
+    // arriving parent's row (position kr, nothing cached) -- one loop, one copy of the code
+#pragma unroll 1
+    for (int a = p; a < kn; ++a) {
+        const bool arr = a == kr;
+        const int ja = arr ? j_add : FID(a + 1);
+        const int c0 = arr ? 0 : p;
+        const double* __restrict__ Ga = P.G + (size_t)ja * V;
+        const double gaa = __ldg(Ga + ja);
+        double d2 = gaa, t = __ldg(Ri + ja);
+        const double* olda = F + SSPS_TRI(a + 1);
+        double* xa = F + SSPS_TRI(a);
+#pragma unroll 1
+        for (int b = 0; b < c0; ++b) { const double l = olda[b]; xa[b] = l; d2 = fma(-l, l, d2); t = fma(-l, Fw[b], t); }
+#pragma unroll 1
+        for (int b = c0; b < a; ++b) xa[b] = __ldg(Ga + FID(b + (b >= p ? 1 : 0)));     // the gathers first, back to back: what follows is a dependent chain
+#pragma unroll 1
+        for (int b = c0; b < a; ++b) {
+            const double* xb = F + SSPS_TRI(b);
+            double s = xa[b];
+#pragma unroll 1
+            for (int m = 0; m < b; ++m) s = fma(-xa[m], xb[m], s);
+            const double l = s * xb[b];
+            xa[b] = l; d2 = fma(-l, l, d2); t = fma(-l, Fw[b], t);
+        }
+        double inv = 0.0, w = 0.0;
+        if (d2 > SSPS_PIVOT_TOL * gaa) { inv = inv_sqrt_ieee(d2); w = t * inv; }
+        else if (d2 != d2 || gaa != gaa) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; }
+        xa[a] = inv; Fw[a] = w;
+        q_new = fma(w, w, q_new);
+    }
+    const double ip_new = __ldg(P.yty + child) - P.shrink * q_new;
+    const float lg_new = fast_lg2((float)ip_new);
+    const bool accept = mh_accept_ool(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1);
+
+    if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
+        int t = 0;
+        #pragma unroll 1
+        for (int b = 0; b < k; ++b) if (b != p) C.xs.T(t++) = (uint16_t)FID(b);
+        if (j_add >= 0) C.xs.T(t++) = (uint16_t)j_add;
+        const double lml_ref = score_set(P, child, C.xs, t, nullptr);
+        const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
+        if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
+    }
+    if (!accept) return 0;
+
+    if (has_rem) {
+        const int credit = rel_now - (int)(w_rem >> 16);
+        if (credit > 0) C.cnt_row[j_rem] += (uint32_t)credit;
+        if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
+    }
+    if (has_add && C.pev && L.n_pev < C.pev_cap)
+        C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
+    L.somc = (L.somc - omc_rem) + omc_add;
+    L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
+    L.k = kn;
+    if (kn <= SSPS_KS) {    // a removal that brings the set back into the SMALL tier (no arrival: kn = kr)
+        #pragma unroll 1
+        for (int a = 0; a < kn; ++a) {
+            const int oa = a + (a >= p ? 1 : 0);
+            int r = (int)Frk[oa];
+            r -= (r > rp) ? 1 : 0;
+            S.W(a) = Fid[oa]; S.set_rank(a, r);
+            const double* row = F + SSPS_TRI(a);
+            #pragma unroll 1
+            for (int m = 0; m <= a; ++m) S.d[(SSPS_TRI(a) + m) * SSPS_BLOCK] = row[m];
+            S.Wv(a) = Fw[a];
+        }
+        L.mode = MODE_SMALL;
+        return 1;
+    }
+    int rj = 0;
+    #pragma unroll 1
+    for (int a = 0; a < kr; ++a) {      // id list: close the gap at p, shift the sorted ranks
+        const int oa = a + (a >= p ? 1 : 0);
+        const uint32_t w = Fid[oa];
+        int r = (int)Frk[oa];
+        r -= (r > rp) ? 1 : 0;
+        if (has_add) { if ((int)(w & 0xffffu) < j_add) ++rj; else ++r; }
+        B.w[a] = w; B.r[a] = (uint16_t)r;
+    }
+    if (has_add) { B.w[kr] = (uint32_t)j_add | ((uint32_t)rel_now << 16); B.r[kr] = (uint16_t)rj; }
+    double* __restrict__ fw = B.fw();
+    #pragma unroll 1
+    for (int a = p; a < kn; ++a) {      // recomputed rows over the arena rows (proposed set's coordinates)
+        const double* xa = F + SSPS_TRI(a);
+        double* __restrict__ dst = B.f + SSPS_TRI(a);
+        #pragma unroll 1
+        for (int m = 0; m <= a; ++m) dst[m] = xa[m];
+        fw[a] = Fw[a];
+    }
+    return 1;
+#undef FID
+}
 
 // ------------------------------------------------------------------------------------------------
 // BIG tier, warp-cooperative.  All arguments are warp-uniform; every lane of the warp must call.
@@ -759,7 +955,7 @@ __device__ __noinline__ double fac_append(const SspsDev& P, const double* __rest
 // acc_kn (per lane): accepted | |S'| << 1 of this lane's move.
 // ------------------------------------------------------------------------------------------------
 template <bool VERIFY>
-__device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const StepDraws& d, Lane L, const SmallAcc& S, const KCtx& C,
+__device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const StepDraws& d, const Move& mv, Lane L, const SmallAcc& S, const KCtx& C,
                                        const int rel_now, unsigned bigm, unsigned pend, int* acc_kn) {
     const int lane = threadIdx.x & 31;
     const int V = P.V;
@@ -773,12 +969,10 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
         const int src = __ffs(bigm) - 1;
         bigm &= bigm - 1;
         const BigRef B = C.big(src);
-        int action = 0, a_ord = 0, r_ord = 0;
-        if (lane == src) select_move(P, child, L.k, d, action, a_ord, r_ord);
         const int k = __shfl_sync(SSPS_FULL, L.k, src);
-        action = __shfl_sync(SSPS_FULL, action, src);
-        a_ord = __shfl_sync(SSPS_FULL, a_ord, src);
-        r_ord = __shfl_sync(SSPS_FULL, r_ord, src);
+        const int action = __shfl_sync(SSPS_FULL, mv.action, src);
+        const int a_ord = __shfl_sync(SSPS_FULL, mv.a_ord, src);
+        const int r_ord = __shfl_sync(SSPS_FULL, mv.r_ord, src);
         const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
         const int kn = k + (has_add ? 1 : 0) - (has_rem ? 1 : 0);
         ++n_big;
@@ -846,15 +1040,14 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
 #endif
         int acc = 0;
         if (lane == src) {
-            double fwd, bwd;
-            move_ratio(P, child, k, action, fwd, bwd);
+            const double fwd = mv.fwd, bwd = mv.bwd;
             const double* __restrict__ omc_i = P.omc + (size_t)V * child;
             double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
             if (has_add) { omc_add = __ldg(omc_i + j_add); dprior = -L.lam * omc_add; }
             if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
             const double ip_new = __ldg(P.yty + child) - P.shrink * q_new;
             const float lg_new = fast_lg2((float)ip_new);
-            acc = mh_accept(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1) ? 1 : 0;
+            acc = mh_accept_ool(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1) ? 1 : 0;
             if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
                 for (int b = 0; b < kn; ++b) C.xs.T(b) = (uint16_t)T.idof(b);
                 const double lml_ref = score_set(P, child, C.xs, kn, nullptr);
@@ -973,14 +1166,48 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
     const int V = P.V;
     const int thin = prm.thinning;
 
-    unsigned long long s_f3 = 0;
-    unsigned s_accp = 0, s_accl = 0, s_k = 0, s_b = 0, s_prop = 0, s_t1 = 0, s_lx = 0;
+    unsigned long long s_f3 = 0, s_midcyc = 0;
+    unsigned s_accp = 0, s_accl = 0, s_k = 0, s_b = 0, s_prop = 0, s_t1 = 0, s_lx = 0, s_mid = 0;
 
+    // A launch with fewer tasks than resident warps (few chains: the time-to-convergence runs) is spread over the SMs:
+    // every CTA keeps only the warps its share of the tasks needs -- a warp alone on its scheduler runs a step about
+    // twice as fast as one of three.
+    const int n_total = __ldg(prm.start + prm.V);
+    const int warps_needed = max(1, (n_total + (int)gridDim.x - 1) / (int)gridDim.x);
+#if SSPS_LOCKSTEP
+    // The warps that share a scheduler (warp id mod 4) pull their tasks together and meet at a named barrier before
+    // every sweep, so that they walk the step's instruction stream side by side and share its fetches.
+    __shared__ int sh_task[4];
+#if SSPS_LOCKSTEP == 2      // the whole CTA in step
+    const int ls_sched = 0, ls_member = threadIdx.x >> 5;
+    const int LS_N = min(SSPS_BLOCK / 32, warps_needed);
+#else
+    const int ls_sched = (threadIdx.x >> 5) & 3, ls_member = threadIdx.x >> 7;
+    const int LS_N = min(SSPS_BLOCK / 128, (warps_needed + 3) / 4);
+#endif
+    if (ls_member >= LS_N) return;
+#define LS_BAR() asm volatile("bar.sync %0, %1;" ::"r"(1 + ls_sched), "r"(32 * LS_N) : "memory")
+#else
+    if ((int)(threadIdx.x >> 5) >= warps_needed) return;
+#define LS_BAR()
+#endif
     for (;;) {
         int task = 0;
+#if SSPS_LOCKSTEP
+        if (ls_member == 0 && lane == 0) sh_task[ls_sched] = atomicAdd(prm.task_counter, LS_N);
+        LS_BAR();
+        const int task_base = sh_task[ls_sched];
+        LS_BAR();
+        if (task_base >= n_total) break;
+        task = task_base + ls_member;
+        const bool task_ok = task < n_total;
+        if (!task_ok) task = task_base;
+#else
         if (lane == 0) task = atomicAdd(prm.task_counter, 1);
         task = __shfl_sync(SSPS_FULL, task, 0);
-        if (task >= __ldg(prm.start + prm.V)) break;
+        if (task >= n_total) break;
+        const bool task_ok = true;
+#endif
         const long long t_start = clock64();
         int lo = 0, hi = prm.V - 1;                     // the rank whose task range holds `task`
         while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (__ldg(prm.start + mid) <= task) lo = mid; else hi = mid - 1; }
@@ -989,7 +1216,7 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
         const int width = 32 / sp;
         const int rel = task - __ldg(prm.start + lo);
         const int chain = (rel / sp) * 32 + (rel % sp) * width + lane;
-        bool live = lane < width && chain < st.n_chains;
+        bool live = task_ok && lane < width && chain < st.n_chains;
         const size_t sidx = (size_t)i * st.nch_pad + (live ? chain : 0);
         const size_t mc = (size_t)(live ? chain : 0) * V + i;
         C.cnt_row = st.counts + mc * V;
@@ -1024,7 +1251,11 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
         int n_lev = 0;
         DrawCarry cy; cy.valid = 0; cy.z = 0.f; cy.w = 0u;
 
+        int rec_done = 0, phase = 0;                        // recorded samples so far, sweeps since the last one (no division per step)
         for (int l = 1; l <= prm.n_local; ++l) {
+#if SSPS_LOCKSTEP
+            if (((l - 1) & (SSPS_LS_EVERY - 1)) == 0) LS_BAR();
+#endif
             StepDraws d;
             d.z = 0.0; d.u_lam = 0.5; d.u_act = 0.5; d.u_add = 0.5; d.u_rem = 0.5; d.u_acc = 0.5;
             if (live) {
@@ -1048,33 +1279,74 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
             }
 
             // ---------------- parent-set move ----------------
-            const int rel_now = ceil_div_i(l, thin) - 1;   // recorded samples of this launch that precede the change
+            const int rel_now = rec_done;                  // recorded samples of this launch that precede the change (= ceil(l / thin) - 1)
             int acc_kn = 0;
-            const unsigned bigm = __ballot_sync(SSPS_FULL, live && L.mode == MODE_BIG);
+            Move mv;
+            mv.action = ACT_ADD; mv.a_ord = 0; mv.r_ord = 0; mv.fwd = 0.0; mv.bwd = 0.0;
+            if (live) {
+                select_move(P, i, L.k, d, mv.action, mv.a_ord, mv.r_ord);
+                move_ratio(P, i, L.k, mv.action, mv.fwd, mv.bwd);
+            }
+            const bool is_big = live && L.mode == MODE_BIG;
+            const bool is_mid = is_big && L.k < SSPS_KM;        // current and proposed set within SSPS_KM rows: the lane on its own
+            const unsigned bigm = __ballot_sync(SSPS_FULL, is_big && !is_mid);
             const unsigned smallm = __ballot_sync(SSPS_FULL, live && L.mode == MODE_SMALL);
             if (live && L.mode == MODE_SMALL) {
                 int kn = 0;
-                const int acc = small_move<VERIFY>(P, i, d, L, S, C, rel_now, smallm, s_t1, kn);
+                const int acc = small_move<VERIFY>(P, i, d, mv, L, S, C, rel_now, smallm, s_t1, kn);
                 acc_kn = acc | (kn << 1);
             }
-            const unsigned pend = __ballot_sync(SSPS_FULL, L.mode == MODE_PROMOTE);
-            if (bigm | pend) L = big_phase<VERIFY>(P, i, d, L, S, C, rel_now, bigm, pend, &acc_kn);
+            unsigned midm = __ballot_sync(SSPS_FULL, is_mid);
+            while (midm) {      // rounds of SSPS_MID_SLOTS lanes: the warp copies their factors into Stage slots, each lane moves its own
+                const long long t_mid = clock64();
+                const int my_slot = __popc(midm & ((1u << lane) - 1u));
+                const bool mine = is_mid && ((midm >> lane) & 1u) && my_slot < SSPS_MID_SLOTS;
+                const unsigned round = __ballot_sync(SSPS_FULL, mine);
+                unsigned rm = round;
+                double* Fs = C.st_smem.t;
+                while (rm) {
+                    const int src_l = __ffs(rm) - 1;
+                    rm &= rm - 1;
+                    const int ks = __shfl_sync(SSPS_FULL, L.k, src_l);
+                    const BigRef Bs = C.big(src_l);
+                    for (int e = lane; e < SSPS_TRI(ks); e += 32) Fs[e] = Bs.f[e];
+                    if (lane < ks) {
+                        Fs[SSPS_TRI(SSPS_KM) + lane] = Bs.fw()[lane];
+                        uint32_t* const Fid = (uint32_t*)(Fs + SSPS_ROWLEN(SSPS_KM));
+                        Fid[lane] = Bs.w[lane];
+                        ((uint16_t*)(Fid + SSPS_KM))[lane] = Bs.r[lane];
+                    }
+                    Fs += SSPS_MID_SLOT;
+                }
+                __syncwarp();
+                if (mine) {
+                    int kn = 0;
+                    const int acc = mid_move<VERIFY>(P, i, d, mv, L, S, C.big(lane), C.st_smem.t + my_slot * SSPS_MID_SLOT, C, rel_now, s_t1, kn);
+                    acc_kn = acc | (kn << 1);
+                    ++s_mid; s_midcyc += (unsigned long long)(clock64() - t_mid);
+                }
+                __syncwarp();
+                midm &= ~round;
+            }
+            if (bigm) L = big_phase<VERIFY>(P, i, d, mv, L, S, C, rel_now, bigm, 0u, &acc_kn);
+            const bool record = ++phase == thin;
+            if (record) { phase = 0; ++rec_done; }
             if (live) {
                 const int kn = acc_kn >> 1;
                 s_accp += (unsigned)(acc_kn & 1);
                 ++s_prop;
                 s_k += (unsigned)kn;
-                s_f3 += (unsigned long long)kn * kn * kn + 6ull * kn * kn + 6ull * kn;
+                s_f3 += (unsigned long long)((unsigned)kn * ((unsigned)kn * ((unsigned)kn + 6u) + 6u));   // k^3 + 6 k^2 + 6 k < 2^32 for k <= 1600
                 s_b += (unsigned)(kn * (kn + 1) / 2 + kn);
                 if (prm.khist) atomicAdd(prm.khist + (kn < 63 ? kn : 63), 1ull);
 
                 // ---------------- thinned recording ----------------
-                if (l % thin == 0) {
+                if (record) {
                     lam_sum += L.lam; lam_sq = fma(L.lam, L.lam, lam_sq);
                     if (prm.lev_val && L.lam != lam_logged) {
                         if (n_lev < prm.lev_cap) {
                             prm.lev_val[mc * prm.lev_cap + n_lev] = L.lam;
-                            prm.lev_idx[mc * prm.lev_cap + n_lev] = (uint16_t)(l / thin);
+                            prm.lev_idx[mc * prm.lev_cap + n_lev] = (uint16_t)rec_done;
                             ++n_lev;
                         }
                         lam_logged = L.lam;
@@ -1102,14 +1374,14 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
             if (prm.lev_n) prm.lev_n[mc] = n_lev;
         }
         __syncwarp();
-        if (lane == 0) atomicAdd(prm.vcost + i, (unsigned long long)(clock64() - t_start));
+        if (lane == 0 && task_ok) atomicAdd(prm.vcost + i, (unsigned long long)(clock64() - t_start));
     }
 
     // stats: warp reduce, one atomic per warp
-    unsigned long long v[8] = {s_accp, s_accl, s_k, s_f3, s_b, s_prop, s_t1, s_lx};
-    const int slot[8] = {ST_ACCP, ST_ACCL, ST_SUMK, ST_F3, ST_BYTES, ST_PROP, ST_TIER1, ST_LAM_EXACT};
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
+    unsigned long long v[10] = {s_accp, s_accl, s_k, s_f3, s_b, s_prop, s_t1, s_lx, s_mid, s_midcyc};
+    const int slot[10] = {ST_ACCP, ST_ACCL, ST_SUMK, ST_F3, ST_BYTES, ST_PROP, ST_TIER1, ST_LAM_EXACT, ST_MID_STEPS, ST_MID_CYCLES};
+#pragma unroll 1
+    for (int e = 0; e < 10; ++e) {
         unsigned long long x = v[e];
         for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(SSPS_FULL, x, o);
         if (lane == 0 && x) atomicAdd(prm.stats + slot[e], x);
