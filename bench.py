@@ -322,8 +322,9 @@ def run_ours(args, rank, world, local_rank):
                 "algorithmic_flops_per_proposal": flops / max(nprop_local, 1),
                 "gather_GBps": gbytes / (k_ms * 1e-3) / 1e9,
                 "kernel_proposals_per_s": nprop_local / (k_ms * 1e-3),
-                "note": "the FP64 fraction is small by construction (33 flops per proposal); the kernel is bound by instruction "
-                        "fetch/issue latency: see issue_slot_utilisation_pct and stall_cycles_per_issue (ncu, profiles/)",
+                "note": "the FP64 fraction is small by construction (33 flops per proposal); the kernel is bound by issue latency "
+                        "(L1/L2 gathers, dependent fp64 chains, the lock-step barrier; instruction fetch before the lock-step): see "
+                        "issue_slot_utilisation_pct and stall_cycles_per_issue (ncu, profiles/)",
                 "ncu": None if ncu is None else {k: ncu[k] for k in ("source", "launch", "issue_slot_utilisation_pct", "fp64_pipe_active_pct",
                                                                     "warp_instructions_per_launch", "stall_cycles_per_issue",
                                                                     "l1_hit_pct", "l2_hit_pct", "registers_per_thread")}}

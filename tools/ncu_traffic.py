@@ -24,7 +24,7 @@ d = {
     "fp64_pipe_active_pct": get("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),
     "l1_hit_pct": get("l1tex__t_sector_hit_rate.pct"), "l2_hit_pct": get("lts__t_sector_hit_rate.pct"),
     "stall_cycles_per_issue": {k: get("smsp__average_warps_issue_stalled_%s_per_issue_active.ratio" % k)
-                               for k in ("no_instruction", "long_scoreboard", "wait", "branch_resolving", "short_scoreboard", "selected")},
+                               for k in ("no_instruction", "long_scoreboard", "wait", "barrier", "branch_resolving", "short_scoreboard", "selected")},
     "registers_per_thread": get("launch__registers_per_thread"),
 }
 json.dump(d, open(out_path, "w"), indent=1)
