@@ -336,15 +336,27 @@ def run_ours(args, rank, world, local_rank):
         h2d = xm_h.nbytes + xp_h.nbytes + pr_h.nbytes
         d2h = V * V * 8 * 2 + V * 8 + 8
 
+        trace = bool(os.environ.get("BENCH_TRACE"))
+
         def e2e_step(seed):
+            tp = [time.perf_counter()]
             s2 = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=S // 4)
             s2.set_stream(stream.cuda_stream)
+            tp.append(time.perf_counter())
             s2.set_data(xm_h, xp_h, pr_h)
+            tp.append(time.perf_counter())
             s2.generate(C, seed=seed, chain_id_offset=rank * C)
+            tp.append(time.perf_counter())
             s2.update_loop(S)
+            tp.append(time.perf_counter())
             mx, _ = s2.psrf(0.5)
             probs, _, _, _ = s2.edge_posterior(0.5)
+            tp.append(time.perf_counter())
             s2.close()
+            tp.append(time.perf_counter())
+            if trace:
+                print("[bench trace] e2e step ms: create %.1f set_data %.1f init_chains %.1f sweeps %.1f psrf+posterior %.1f close %.1f"
+                      % tuple(1e3 * (tp[e + 1] - tp[e]) for e in range(6)), file=sys.stderr)
             return probs
 
         for w in range(min(args.warmup, 2)):

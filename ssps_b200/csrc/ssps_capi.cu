@@ -17,6 +17,9 @@
 
 #include <algorithm>
 #include <chrono>
+#include <map>
+#include <mutex>
+#include <utility>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -53,6 +56,77 @@ int fail(int code, const char* fmt, ...) {
         if (s_ != SSPS_OK) return s_; \
     } while (0)
 
+// Device blocks are recycled through a process-wide cache keyed by (device, size): cudaMalloc of the 100 MB-class buffers
+// (tally snapshots, factor arena) costs 2..100 ms at random, inside run_sweeps and between the handles of back-to-back runs
+// (measured: bench steps of 83 ms instead of 39).  A released block goes back to the cache; the same shapes come again.
+// Ordering: a block is only ever released by the handle that used it, after that handle's stream work on it was enqueued;
+// re-use inside the same handle is stream-ordered, and ssps_destroy synchronises the stream before its blocks are released.
+thread_local cudaStream_t g_stream = nullptr;     // stream of the handle the calling thread is working on (bind)
+
+class BlockCache {
+public:
+    static BlockCache& get() { static BlockCache c; return c; }
+    cudaError_t take(size_t bytes, void** out) {
+        int dev = 0; cudaGetDevice(&dev);
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            auto it = free_.find({dev, bytes});
+            if (it != free_.end()) {
+                auto& v = it->second;
+                for (size_t e = v.size(); e-- > 0;) {
+                    // usable once the work that was pending on the block at its release has completed
+                    if (v[e].ev && cudaEventQuery(v[e].ev) != cudaSuccess) { cudaGetLastError(); continue; }
+                    if (v[e].ev) cudaEventDestroy(v[e].ev);
+                    *out = v[e].p; v.erase(v.begin() + (long)e); cached_ -= bytes;
+                    return cudaSuccess;
+                }
+            }
+        }
+        cudaError_t e = cudaMalloc(out, bytes);
+        if (e != cudaSuccess) {         // give the cache back to the driver and try once more
+            cudaGetLastError();
+            trim(dev);
+            e = cudaMalloc(out, bytes);
+        }
+        return e;
+    }
+    void give(void* p, size_t bytes) {
+        int dev = 0; cudaGetDevice(&dev);
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            if (cached_ + bytes <= cap_) {
+                Block b; b.p = p; b.ev = nullptr;
+                if (cudaEventCreateWithFlags(&b.ev, cudaEventDisableTiming) == cudaSuccess) {
+                    if (cudaEventRecord(b.ev, g_stream) != cudaSuccess) { cudaGetLastError(); cudaEventDestroy(b.ev); b.ev = nullptr; cudaStreamSynchronize(g_stream); }
+                } else { cudaGetLastError(); b.ev = nullptr; cudaStreamSynchronize(g_stream); }
+                free_[{dev, bytes}].push_back(b); cached_ += bytes;
+                return;
+            }
+        }
+        cudaFree(p);
+    }
+    size_t cached_bytes(int dev) {
+        std::lock_guard<std::mutex> g(mu_);
+        size_t t = 0;
+        for (auto& kv : free_) if (kv.first.first == dev) t += kv.first.second * kv.second.size();
+        return t;
+    }
+    void trim(int dev) {
+        std::lock_guard<std::mutex> g(mu_);
+        for (auto& kv : free_)
+            if (kv.first.first == dev) {
+                for (auto& b : kv.second) { if (b.ev) cudaEventDestroy(b.ev); cudaFree(b.p); cached_ -= kv.first.second; }
+                kv.second.clear();
+            }
+    }
+private:
+    struct Block { void* p; cudaEvent_t ev; };
+    std::mutex mu_;
+    std::map<std::pair<int, size_t>, std::vector<Block>> free_;
+    size_t cached_ = 0;
+    size_t cap_ = (size_t)96 << 30;     // bytes kept at most (a B200 has 180 GB)
+};
+
 template <class T>
 struct DevBuf {
     T* p = nullptr;
@@ -66,12 +140,14 @@ struct DevBuf {
         return *this;
     }
     ~DevBuf() { release(); }
-    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    void release() { if (p) BlockCache::get().give(p, n * sizeof(T)); p = nullptr; n = 0; }
     cudaError_t alloc(size_t count) {
-        release();
         if (count == 0) count = 1;
-        cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
-        if (e == cudaSuccess) n = count; else p = nullptr;
+        if (p && n == count) return cudaSuccess;        // same shape again: keep the block (contents are undefined either way)
+        release();
+        void* q = nullptr;
+        cudaError_t e = BlockCache::get().take(count * sizeof(T), &q);
+        if (e == cudaSuccess) { p = (T*)q; n = count; } else p = nullptr;
         return e;
     }
     size_t bytes() const { return n * sizeof(T); }
@@ -134,8 +210,9 @@ struct ssps_handle {
     // ---- snapshots for split-PSRF / burn-in (K4) ----
     int64_t snap_grid = 0;          // in recorded samples; 0 = disabled
     size_t snap_budget_bytes = 0;
+    std::vector<Snapshot> spare;    // allocated ahead: no cudaMalloc between the launches of run_sweeps
     std::vector<Snapshot> snaps;    // ascending n, all multiples of snap_grid
-    DevBuf<double> sums_scratch, psrf_scratch;
+    DevBuf<double> sums_scratch, psrf_scratch, psrf_partial;
     DevBuf<unsigned long long> max_bits;
 
     // ---- change-point log (small runs) ----
@@ -164,6 +241,7 @@ namespace {
 int bind(ssps_handle* h) {
     if (!h) return fail(SSPS_ERR_INVALID, "null handle");
     CK(cudaSetDevice(h->device));
+    g_stream = h->stream;
     return SSPS_OK;
 }
 
@@ -276,7 +354,7 @@ int finish_data(ssps_handle* h, const double* prior_host) {
     h->has_data = true;
     // any chains belong to the previous data set
     h->n_chains = 0;
-    h->snaps.clear();
+    h->snaps.clear(); h->spare.clear();
     return SSPS_OK;
 }
 
@@ -326,13 +404,16 @@ void ssps_destroy(ssps_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    g_stream = h->stream;
     delete h;
+    g_stream = nullptr;
 }
 
 int ssps_set_stream(ssps_handle* h, void* cuda_stream) {
     CKS(bind(h));
     CK(cudaStreamSynchronize(h->stream));
     h->stream = (cudaStream_t)cuda_stream;
+    g_stream = h->stream;
     return SSPS_OK;
 }
 
@@ -488,11 +569,22 @@ int ssps_score(ssps_handle* h, int32_t n_sets, const int32_t* child, const int32
 // ================================================================================================
 namespace {
 
+int reserve_snapshots(ssps_handle* h, size_t count);
+
+// K4 reductions over chains: enough (edge, chain-chunk) threads to fill the GPU; one chunk when V^2 alone does
+void chain_chunks(const ssps_handle* h, size_t vv, int& chunks, int& chunk_len) {
+    const size_t want = (size_t)h->sm_count * 2048;
+    chunks = (int)std::max<size_t>(1, std::min<size_t>((want + vv - 1) / vv, (size_t)std::max(1, h->n_chains / 32)));
+    chunks = std::min(chunks, 64);
+    chunk_len = (h->n_chains + chunks - 1) / chunks;
+    chunks = (h->n_chains + chunk_len - 1) / chunk_len;
+}
+
 int alloc_chains(ssps_handle* h, int n_chains) {
     const int V = h->V;
     const size_t vv = (size_t)V * V;
     h->n_chains = 0;
-    h->snaps.clear();
+    h->snaps.clear(); h->spare.clear();
     h->nch_pad = ((n_chains + 31) / 32) * 32;
     int kcap = h->cfg.max_indegree > 0 ? h->cfg.max_indegree : std::min(V, 64);
     h->kcap = std::min(kcap, V);
@@ -578,11 +670,13 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     h->snap_grid = h->cfg.psrf_grid == 0 ? 250 : (h->cfg.psrf_grid < 0 ? 0 : h->cfg.psrf_grid);
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
+    free_b += BlockCache::get().cached_bytes(h->device);
     h->snap_budget_bytes = free_b / 4;
 
     h->cp_parent.clear(); h->cp_lambda.clear(); h->cp_present.clear(); h->cp_lambda_last.clear();
     h->pev_cap = h->lev_cap = 0;
     h->n_chains = n_chains;
+    CKS(reserve_snapshots(h, 32));
     return SSPS_OK;
 }
 
@@ -691,6 +785,23 @@ int changepoints_drain(ssps_handle* h, int64_t rec_base) {
     return SSPS_OK;
 }
 
+// `count` more snapshot buffers ahead of need (bounded by the budget): cudaMalloc of these 100 MB-class blocks takes
+// 2..100 ms at random, which must not fall between the launches of run_sweeps
+int reserve_snapshots(ssps_handle* h, size_t count) {
+    if (h->snap_grid <= 0 || h->n_chains <= 0) return SSPS_OK;
+    const size_t vv = (size_t)h->V * h->V, nc = (size_t)h->n_chains;
+    const size_t per = vv * nc * sizeof(uint32_t) + 2 * (size_t)h->V * nc * sizeof(double);
+    const size_t have = h->snaps.size() + h->spare.size();
+    const size_t room = h->snap_budget_bytes / std::max<size_t>(per, 1);
+    count = std::min(count, room > have ? room - have : 0);
+    for (size_t e = 0; e < count; ++e) {
+        Snapshot sn;
+        CK(sn.counts.alloc(vv * nc)); CK(sn.lam_sum.alloc((size_t)h->V * nc)); CK(sn.lam_sq.alloc((size_t)h->V * nc));
+        h->spare.push_back(std::move(sn));
+    }
+    return SSPS_OK;
+}
+
 int take_snapshot(ssps_handle* h) {
     const size_t vv = (size_t)h->V * h->V;
     const size_t per = vv * h->n_chains * sizeof(uint32_t) + 2 * (size_t)h->V * h->n_chains * sizeof(double);
@@ -698,17 +809,27 @@ int take_snapshot(ssps_handle* h) {
     while (h->snap_grid > 0 && (h->snaps.size() + 1) * per > h->snap_budget_bytes && h->snaps.size() >= 2) {
         h->snap_grid *= 2;
         std::vector<Snapshot> kept;
-        for (auto& s : h->snaps)
+        for (auto& s : h->snaps) {
             if (s.n % h->snap_grid == 0) kept.push_back(std::move(s));
+            else h->spare.push_back(std::move(s));      // same stream: safe to overwrite in order
+        }
         h->snaps.swap(kept);
     }
     if (h->snap_grid == 0 || h->samples_recorded % h->snap_grid != 0) return SSPS_OK;
+    if (h->spare.empty()) {
+        const auto ta = std::chrono::steady_clock::now();
+        CKS(reserve_snapshots(h, 16));
+        if (getenv("SSPS_TRACE"))
+            fprintf(stderr, "[ssps trace] snapshot refill %.1f ms (n = %lld)\n",
+                    1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - ta).count(), (long long)h->samples_recorded);
+    }
     Snapshot sn;
+    if (!h->spare.empty()) { sn = std::move(h->spare.back()); h->spare.pop_back(); }
+    else { CK(sn.counts.alloc(vv * h->n_chains)); CK(sn.lam_sum.alloc((size_t)h->V * h->n_chains)); CK(sn.lam_sq.alloc((size_t)h->V * h->n_chains)); }
     sn.n = h->samples_recorded;
-    CK(sn.counts.alloc(vv * h->n_chains)); CK(sn.lam_sum.alloc((size_t)h->V * h->n_chains)); CK(sn.lam_sq.alloc((size_t)h->V * h->n_chains));
-    CK(cudaMemcpyAsync(sn.counts.p, h->counts.p, sn.counts.bytes(), cudaMemcpyDeviceToDevice, h->stream));
-    CK(cudaMemcpyAsync(sn.lam_sum.p, h->lam_sum.p, sn.lam_sum.bytes(), cudaMemcpyDeviceToDevice, h->stream));
-    CK(cudaMemcpyAsync(sn.lam_sq.p, h->lam_sq.p, sn.lam_sq.bytes(), cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpyAsync(sn.counts.p, h->counts.p, vv * h->n_chains * sizeof(uint32_t), cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpyAsync(sn.lam_sum.p, h->lam_sum.p, (size_t)h->V * h->n_chains * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpyAsync(sn.lam_sq.p, h->lam_sq.p, (size_t)h->V * h->n_chains * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
     h->snaps.push_back(std::move(sn));
     return SSPS_OK;
 }
@@ -748,6 +869,9 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
         // launch boundary = next snapshot point (or the default batch), capped by the rel-index width
         int64_t rec = std::min<int64_t>((n_sweeps - done) / thinning, std::min(max_rec, dflt_rec));
         if (h->snap_grid > 0) rec = std::min(rec, h->snap_grid - h->samples_recorded % h->snap_grid);
+        // no measured task costs yet: a short calibration launch, so that the scheduler can split the heavy vertices for the rest
+        // of the batch (the first 100-sweep launch of a fresh handle ran 25 % longer than the later ones)
+        if (!h->have_cost && !replay_host && rec > 24) rec = 8;
         const int n_local = (int)(rec * thinning);
         MhParams prm{};
         prm.sweep0 = h->sweeps_done; prm.n_local = n_local; prm.thinning = thinning;
@@ -813,6 +937,11 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
         }
     }
     CK(cudaStreamSynchronize(h->stream));
+    if (getenv("SSPS_TRACE")) {
+        const double ms = 1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        float kms = 0; for (size_t e = 0; e < ev_used; ++e) { float m1 = 0; cudaEventElapsedTime(&m1, h->ev_pool[e].first, h->ev_pool[e].second); kms += m1; }
+        if (ms > 1.5 * kms + 2.0) fprintf(stderr, "[ssps trace] run_sweeps %.1f ms wall, %.1f ms in the MH kernel (%lld sweeps)\n", ms, kms, (long long)done);
+    }
     for (size_t e = 0; e < ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
     if (sweeps_done_out) *sweeps_done_out = done;
     unsigned long long overflow = 0;
@@ -952,7 +1081,10 @@ int ssps_edge_counts(ssps_handle* h, double* counts_child_major, int64_t* n_samp
     if (counts_child_major) {
         DevBuf<double> out;
         CK(out.alloc(vv));
-        edge_sum_kernel<<<div_up(vv, 256), 256, 0, h->stream>>>(h->counts.p, nullptr, h->n_chains, vv, out.p);
+        int chunks = 1, chunk_len = h->n_chains;
+        chain_chunks(h, vv, chunks, chunk_len);
+        CK(cudaMemsetAsync(out.p, 0, out.bytes(), h->stream));
+        edge_sum_kernel<<<dim3(div_up(vv, 256), chunks), 256, 0, h->stream>>>(h->counts.p, nullptr, h->n_chains, vv, chunk_len, out.p);
         CKS(launch_ok(h, "edge_sum"));
         CKS(download(h, counts_child_major, out.p, vv));
         CK(cudaStreamSynchronize(h->stream));
@@ -987,7 +1119,10 @@ int ssps_edge_posterior(ssps_handle* h, double burnin, double* probs_child_major
     if (probs_child_major) {
         DevBuf<double> out;
         CK(out.alloc(vv));
-        edge_sum_kernel<<<div_up(vv, 256), 256, 0, h->stream>>>(h->counts.p, lo ? lo->counts.p : nullptr, h->n_chains, vv, out.p);
+        int chunks = 1, chunk_len = h->n_chains;
+        chain_chunks(h, vv, chunks, chunk_len);
+        CK(cudaMemsetAsync(out.p, 0, out.bytes(), h->stream));
+        edge_sum_kernel<<<dim3(div_up(vv, 256), chunks), 256, 0, h->stream>>>(h->counts.p, lo ? lo->counts.p : nullptr, h->n_chains, vv, chunk_len, out.p);
         CKS(launch_ok(h, "edge_sum"));
         CKS(download(h, probs_child_major, out.p, vv));
         CK(cudaStreamSynchronize(h->stream));
@@ -996,7 +1131,7 @@ int ssps_edge_posterior(ssps_handle* h, double burnin, double* probs_child_major
     if (lambda_mean) {
         DevBuf<double> out;
         CK(out.alloc(h->V));
-        lam_sum_kernel<<<div_up((size_t)h->V, 128), 128, 0, h->stream>>>(h->lam_sum.p, lo ? lo->lam_sum.p : nullptr, h->n_chains, h->V, out.p);
+        lam_sum_kernel<<<h->V, 256, 0, h->stream>>>(h->lam_sum.p, lo ? lo->lam_sum.p : nullptr, h->n_chains, h->V, out.p);
         CKS(launch_ok(h, "lam_sum"));
         CKS(download(h, lambda_mean, out.p, (size_t)h->V));
         CK(cudaStreamSynchronize(h->stream));
@@ -1043,9 +1178,20 @@ int ssps_psrf_sums(ssps_handle* h, double burnin, double* sums, int32_t on_devic
     const uint32_t* c_len = S_len ? S_len->counts.p : h->counts.p;
     const double* ls_len = S_len ? S_len->lam_sum.p : h->lam_sum.p;
     const double* lq_len = S_len ? S_len->lam_sq.p : h->lam_sq.p;
-    psrf_sums_kernel<<<div_up(vv, 256), 256, 0, h->stream>>>(c_len, S_s->counts.p, S_b ? S_b->counts.p : nullptr, h->n_chains, vv, N1, N2, dst);
-    CKS(launch_ok(h, "psrf_sums"));
-    psrf_lambda_sums_kernel<<<div_up((size_t)V, 128), 128, 0, h->stream>>>(ls_len, S_s->lam_sum.p, S_b ? S_b->lam_sum.p : nullptr, lq_len,
+    {
+        int chunks = 1, chunk_len = h->n_chains;
+        chain_chunks(h, vv, chunks, chunk_len);
+        double* part = dst;
+        if (chunks > 1) { CK(h->psrf_partial.alloc((size_t)chunks * 3 * vv)); part = h->psrf_partial.p; }
+        psrf_sums_kernel<<<dim3(div_up(vv, 256), chunks), 256, 0, h->stream>>>(c_len, S_s->counts.p, S_b ? S_b->counts.p : nullptr, h->n_chains, vv,
+                                                                                N1, N2, chunk_len, part);
+        CKS(launch_ok(h, "psrf_sums"));
+        if (chunks > 1) {
+            psrf_sums_reduce_kernel<<<div_up(3 * vv, 256), 256, 0, h->stream>>>(part, chunks, 3 * vv, dst);
+            CKS(launch_ok(h, "psrf_sums_reduce"));
+        }
+    }
+    psrf_lambda_sums_kernel<<<V, 256, 0, h->stream>>>(ls_len, S_s->lam_sum.p, S_b ? S_b->lam_sum.p : nullptr, lq_len,
                                                                         S_s->lam_sq.p, S_b ? S_b->lam_sq.p : nullptr, h->n_chains, V, N1, N2,
                                                                         dst + 3 * vv);
     CKS(launch_ok(h, "psrf_lambda_sums"));

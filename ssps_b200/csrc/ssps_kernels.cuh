@@ -367,36 +367,57 @@ __global__ void state_lml_kernel(SspsDev P, ChainState st, int chain, double* __
 // K4: tallies -> posterior / split-PSRF sufficient statistics
 // counts snapshots are [chain][V*V] uint32 cumulative; c_b / c_s may be NULL (= all zero).
 // ------------------------------------------------------------------------------------------------
+// Chains are split into gridDim.y chunks (a thread per edge alone leaves V^2 threads walking all the chains: 11 ms at
+// V = 100 x 4096 chains).  The tallies are integers below 2^53, so the double atomics are exact and order-independent.
+// `out` must be zeroed.
 __global__ void edge_sum_kernel(const uint32_t* __restrict__ c_hi, const uint32_t* __restrict__ c_lo, int n_chains,
-                                size_t vv, double* __restrict__ out) {
+                                size_t vv, int chunk_len, double* __restrict__ out) {
     size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= vv) return;
+    const int c0 = blockIdx.y * chunk_len, c1 = min(n_chains, c0 + chunk_len);
     unsigned long long s = 0;
-    for (int c = 0; c < n_chains; ++c) {
+    for (int c = c0; c < c1; ++c) {
         uint32_t hi = c_hi[(size_t)c * vv + e];
         uint32_t lo = c_lo ? c_lo[(size_t)c * vv + e] : 0u;
         s += (unsigned long long)(hi - lo);
     }
-    out[e] = (double)s;
+    if (s) atomicAdd(out + e, (double)s);
 }
 
-__global__ void lam_sum_kernel(const double* __restrict__ s_hi, const double* __restrict__ s_lo, int n_chains, int V,
-                               double* __restrict__ out) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= V) return;
-    double s = 0.0;
-    for (int c = 0; c < n_chains; ++c) s += s_hi[(size_t)c * V + i] - (s_lo ? s_lo[(size_t)c * V + i] : 0.0);
-    out[i] = s;
+// block-wide sum of up to three values per thread, fixed tree (deterministic); result valid in thread 0.  blockDim.x = 256
+__device__ __forceinline__ void block_sum3(double& a, double& b, double& c) {
+    __shared__ double sh[3][8];
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_down_sync(0xffffffffu, a, o); b += __shfl_down_sync(0xffffffffu, b, o); c += __shfl_down_sync(0xffffffffu, c, o);
+    }
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { sh[0][w] = a; sh[1][w] = b; sh[2][w] = c; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        a = sh[0][0]; b = sh[1][0]; c = sh[2][0];
+        for (int e = 1; e < (int)(blockDim.x >> 5); ++e) { a += sh[0][e]; b += sh[1][e]; c += sh[2][e]; }
+    }
+}
+
+// one block per vertex, threads stride over the chains (a thread per vertex walked 4096 chains alone: 2 ms)
+__global__ void __launch_bounds__(256) lam_sum_kernel(const double* __restrict__ s_hi, const double* __restrict__ s_lo, int n_chains, int V,
+                                                      double* __restrict__ out) {
+    const int i = blockIdx.x;
+    double s = 0.0, z1 = 0.0, z2 = 0.0;
+    for (int c = threadIdx.x; c < n_chains; c += blockDim.x) s += s_hi[(size_t)c * V + i] - (s_lo ? s_lo[(size_t)c * V + i] : 0.0);
+    block_sum3(s, z1, z2);
+    if (threadIdx.x == 0) out[i] = s;
 }
 
 // per edge: sum over half-chains of m, m^2, m(1-m)N/(N-1)   (postprocess_samples.jl:99-138)
 __global__ void psrf_sums_kernel(const uint32_t* __restrict__ c_len, const uint32_t* __restrict__ c_s,
                                  const uint32_t* __restrict__ c_b, int n_chains, size_t vv, double N1, double N2,
-                                 double* __restrict__ sums) {
+                                 int chunk_len, double* __restrict__ partial /* [chunk][3][vv]; one chunk: the sums themselves */) {
     size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= vv) return;
+    const int c0 = blockIdx.y * chunk_len, c1 = min(n_chains, c0 + chunk_len);
     double sm = 0.0, sm2 = 0.0, sv = 0.0;
-    for (int c = 0; c < n_chains; ++c) {
+    for (int c = c0; c < c1; ++c) {
         const uint32_t xl = c_len[(size_t)c * vv + e];
         const uint32_t xs = c_s[(size_t)c * vv + e];
         const uint32_t xb = c_b ? c_b[(size_t)c * vv + e] : 0u;
@@ -406,18 +427,26 @@ __global__ void psrf_sums_kernel(const uint32_t* __restrict__ c_len, const uint3
         sv += m1 * (1.0 - m1) * N1 / (N1 - 1.0);
         sv += m2 * (1.0 - m2) * N2 / (N2 - 1.0);
     }
-    sums[e] = sm; sums[vv + e] = sm2; sums[2 * vv + e] = sv;
+    double* __restrict__ dst = partial + (size_t)blockIdx.y * 3 * vv;
+    dst[e] = sm; dst[vv + e] = sm2; dst[2 * vv + e] = sv;
+}
+// chunk partials -> sums, chunks added in ascending order (deterministic)
+__global__ void psrf_sums_reduce_kernel(const double* __restrict__ partial, int chunks, size_t n3 /* 3 vv */, double* __restrict__ sums) {
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n3) return;
+    double s = 0.0;
+    for (int ch = 0; ch < chunks; ++ch) s += partial[(size_t)ch * n3 + e];
+    sums[e] = s;
 }
 
 // lambda_i: per half-chain mean and corrected variance from cumulative sums / sums of squares
-__global__ void psrf_lambda_sums_kernel(const double* __restrict__ s_len, const double* __restrict__ s_s,
+__global__ void __launch_bounds__(256) psrf_lambda_sums_kernel(const double* __restrict__ s_len, const double* __restrict__ s_s,
                                         const double* __restrict__ s_b, const double* __restrict__ q_len,
                                         const double* __restrict__ q_s, const double* __restrict__ q_b, int n_chains,
                                         int V, double N1, double N2, double* __restrict__ sums /* 3*V */) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= V) return;
+    const int i = blockIdx.x;
     double sm = 0.0, sm2 = 0.0, sv = 0.0;
-    for (int c = 0; c < n_chains; ++c) {
+    for (int c = threadIdx.x; c < n_chains; c += blockDim.x) {
         const size_t e = (size_t)c * V + i;
         const double sb = s_b ? s_b[e] : 0.0, qb = q_b ? q_b[e] : 0.0;
         const double a1 = s_s[e] - sb, a2 = s_len[e] - s_s[e];
@@ -426,7 +455,8 @@ __global__ void psrf_lambda_sums_kernel(const double* __restrict__ s_len, const 
         const double v1 = (b1 - N1 * m1 * m1) / (N1 - 1.0), v2 = (b2 - N2 * m2 * m2) / (N2 - 1.0);
         sm += m1 + m2; sm2 += m1 * m1 + m2 * m2; sv += fmax(v1, 0.0) + fmax(v2, 0.0);
     }
-    sums[i] = sm; sums[V + i] = sm2; sums[2 * V + i] = sv;
+    block_sum3(sm, sm2, sv);
+    if (threadIdx.x == 0) { sums[i] = sm; sums[V + i] = sm2; sums[2 * V + i] = sv; }
 }
 
 // psrf = sqrt(((n-1)/n W + B/n) / W),  B = n * sum (m - mbar)^2 / H (1/H: quirk Q6), W = sum var / H

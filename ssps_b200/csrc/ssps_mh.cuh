@@ -191,9 +191,9 @@ struct Stage {
 #define SSPS_SMEM_BYTES ((size_t)SSPS_SMEM_DOUBLES * 8 + (size_t)SSPS_SMEM_WORDS * 4 + (size_t)(SSPS_BLOCK / 32) * SSPS_KST * 2 + (size_t)SSPS_KS * SSPS_BLOCK)
 
 struct Lane {
-    double lam, somc, q, ip, nrmf;   // nrmf: screening value of the prior normaliser at lam
+    double lam, somc, ip, nrmf;      // nrmf: screening value of the prior normaliser at lam
     float lg_ip;                     // lg2(ip), screening
-    int k, mode, n_pev, pend_j;      // pend_j: the parent whose accepted arrival outgrew the SMALL tier
+    int k, mode, n_pev;
 };
 
 struct MhParams {
@@ -220,10 +220,11 @@ struct MhParams {
     double* lev_val; uint16_t* lev_idx; int* lev_n; int lev_cap;
 };
 
-struct KCtx {       // per-lane pointers
-    double* big_d0; uint32_t* big_w0; uint16_t* big_r0;    // arena block of lane 0 of this warp
-    Stage st_smem, st_glob;                                // this warp's working copies
-    Scratch xs;
+struct KCtx {       // what the tiers need besides the lane state.  Pointers of the rare tiers (arena, global Stage, verify
+                    // scratch) are formed on demand from the launch parameters: carried in registers they spilled the hot loop
+    const MhParams* prm;   // the kernel's __grid_constant__ parameter block
+    int wbase;             // global thread index of lane 0 of this warp
+    Stage st_smem;         // this warp's shared-memory Stage
     double yty;            // y_i' y_i of this task's vertex
     uint32_t* cnt_row;     // counts + mc * V
     uint32_t* pev;         // pev + mc * pev_cap (nullable)
@@ -231,11 +232,24 @@ struct KCtx {       // per-lane pointers
     unsigned long long* stats;
     __device__ __forceinline__ BigRef big(int ln) const {
         BigRef b;
-        b.f = big_d0 + (size_t)ln * SSPS_ROWLEN(kcap);
-        b.w = big_w0 + (size_t)ln * kcap; b.r = big_r0 + (size_t)ln * kcap; b.kcap = kcap;
+        const size_t t = (size_t)(wbase + ln);
+        b.f = prm->big_d + t * SSPS_ROWLEN(kcap);
+        b.w = prm->big_w + t * kcap; b.r = prm->big_r + t * kcap; b.kcap = kcap;
         return b;
     }
-    __device__ __forceinline__ Stage stage(int rows) const { return rows <= SSPS_KST ? st_smem : st_glob; }
+    __device__ __forceinline__ Stage stage(int rows) const {
+        if (rows <= SSPS_KST) return st_smem;
+        Stage g;
+        const size_t w = (size_t)(wbase >> 5);
+        g.t = prm->scr_d + w * SSPS_ROWLEN(kcap); g.tw = g.t + SSPS_TRI(kcap);
+        g.id = prm->scr_w + w * kcap; g.rk = prm->scr_r + w * kcap;
+        return g;
+    }
+    __device__ __forceinline__ Scratch xs_of(int ln) const {
+        Scratch x;
+        x.d = prm->x_d + (wbase + ln); x.t = prm->x_t + (wbase + ln); x.stride = prm->stride; x.kcap = kcap;
+        return x;
+    }
 };
 
 __device__ __forceinline__ int ceil_div_i(int a, int b) { return (a + b - 1) / b; }
@@ -359,7 +373,7 @@ __device__ __noinline__ int mh_accept_exact(const double log1pn, const double dn
 
 __device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
                                           const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
-                                          const double ip_new, const float lg_new, const double u_acc, unsigned& n_t1) {
+                                          const double ip_new, const float lg_new, const double u_acc, unsigned long long* stats) {
     const float lgu = fast_lg2((float)u_acc);
     const double hn = 0.5 * P.dn;
     const double base = ((dprior - fwd) + bwd) - 0.5 * (double)(kn - k) * P.log1pn;
@@ -367,7 +381,7 @@ __device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, co
     const double marg = 1.2e-6 * ((double)fabsf(lgu) + 1.0 + hn * ((double)(fabsf(lg_new) + fabsf(lg_ip_cur)) + 2.0)) + 1e-9 * fabs(base) + 1e-6;
     bool accept = diff < 0.0;
     if (!(u_acc > 1e-30 && fabs(diff) > marg)) {        // too close (or NaN): the reference-order fp64 test
-        ++n_t1;
+        atomicAdd(stats + ST_TIER1, 1ull);      // rare (5e-6 per proposal): no counter register in the hot loop
 #ifdef SSPS_ACCEPT_OOL
         accept = mh_accept_exact(P.log1pn, P.dn, action, k, kn, dprior, fwd, bwd, ip_cur, ip_new, u_acc) != 0;
 #else
@@ -384,12 +398,12 @@ __device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, co
 // out-of-line copy for the rare tiers (mid_move, big_phase): 320 instructions per inlined instance
 __device__ __noinline__ bool mh_accept_ool(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
                                            const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
-                                           const double ip_new, const float lg_new, const double u_acc, unsigned& n_t1) {
-    return mh_accept(P, action, k, kn, dprior, fwd, bwd, ip_cur, lg_ip_cur, ip_new, lg_new, u_acc, n_t1);
+                                           const double ip_new, const float lg_new, const double u_acc, unsigned long long* stats) {
+    return mh_accept(P, action, k, kn, dprior, fwd, bwd, ip_cur, lg_ip_cur, ip_new, lg_new, u_acc, stats);
 }
 
 __device__ __forceinline__ void lane_set_q(const SspsDev& P, int child, Lane& L, double q) {
-    L.q = q; L.ip = __ldg(P.yty + child) - P.shrink * q; L.lg_ip = fast_lg2((float)L.ip);
+    L.ip = __ldg(P.yty + child) - P.shrink * q; L.lg_ip = fast_lg2((float)L.ip);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -439,7 +453,7 @@ struct Move { int action, a_ord, r_ord; double fwd, bwd; };
 
 template <bool VERIFY>
 __device__ __forceinline__ int small_move(const SspsDev& P, const int child, const StepDraws& d, const Move& mv, Lane& L, const SmallAcc& S,
-                                          const KCtx& C, const int rel_now, const unsigned peers, unsigned& n_t1, int& kn_out) {
+                                          const KCtx& C, const int rel_now, const unsigned peers, int& kn_out) {
     constexpr int KS = SSPS_KS;
     const int V = P.V, k = L.k;
     const int action = mv.action, a_ord = mv.a_ord, r_ord = mv.r_ord;
@@ -582,14 +596,15 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     }
     const double ip_new = C.yty - P.shrink * q_new;
     const float lg_new = fast_lg2((float)ip_new);
-    const bool accept = mh_accept(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1);
+    const bool accept = mh_accept(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats);
 
     if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
         int t = 0;
+        const Scratch xs = C.xs_of(threadIdx.x & 31);
 #pragma unroll
-        for (int b = 0; b < KS; ++b) if (b < k && b != p) C.xs.T(t++) = (uint16_t)(idw[b] & 0xffffu);
-        if (j_add >= 0) C.xs.T(t++) = (uint16_t)j_add;
-        const double lml_ref = score_set(P, child, C.xs, t, nullptr);
+        for (int b = 0; b < KS; ++b) if (b < k && b != p) xs.T(t++) = (uint16_t)(idw[b] & 0xffffu);
+        if (j_add >= 0) xs.T(t++) = (uint16_t)j_add;
+        const double lml_ref = score_set(P, child, xs, t, nullptr);
         const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
         if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
     }
@@ -604,7 +619,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     if (has_add && C.pev && L.n_pev < C.pev_cap)
         C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
     L.somc = (L.somc - omc_rem) + omc_add;
-    L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
+    L.ip = ip_new; L.lg_ip = lg_new;
     if (kn > KS) {      // an arrival that outgrows shared memory (k == KS, pure add): the lane moves itself to the BIG tier
         const BigRef B = C.big(threadIdx.x & 31);
         for (int e = 0; e < SSPS_TRI(KS); ++e) B.f[e] = S.d[e * SSPS_BLOCK];
@@ -672,7 +687,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
 #define SSPS_MID_SLOTS (SSPS_ROWLEN(SSPS_KST) / SSPS_MID_SLOT)
 template <bool VERIFY>
 __device__ __noinline__ int mid_move(const SspsDev& P, const int child, const StepDraws& d, const Move& mv, Lane& L, const SmallAcc& S, const BigRef B,
-                                     double* F, const KCtx& C, const int rel_now, unsigned& n_t1, int& kn_out) {
+                                     double* F, const KCtx& C, const int rel_now, int& kn_out) {
     const int V = P.V, k = L.k;
     const uint32_t* Fid = (const uint32_t*)(F + SSPS_ROWLEN(SSPS_KM));      // id | rel << 16, arrival order (the CURRENT set throughout)
     const uint16_t* Frk = (const uint16_t*)(Fid + SSPS_KM);                 // sorted ranks
@@ -741,14 +756,15 @@ __device__ __noinline__ int mid_move(const SspsDev& P, const int child, const St
     }
     const double ip_new = C.yty - P.shrink * q_new;
     const float lg_new = fast_lg2((float)ip_new);
-    const bool accept = mh_accept_ool(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1);
+    const bool accept = mh_accept_ool(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats);
 
     if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
         int t = 0;
-        #pragma unroll 1
-        for (int b = 0; b < k; ++b) if (b != p) C.xs.T(t++) = (uint16_t)FID(b);
-        if (j_add >= 0) C.xs.T(t++) = (uint16_t)j_add;
-        const double lml_ref = score_set(P, child, C.xs, t, nullptr);
+        const Scratch xs = C.xs_of(threadIdx.x & 31);
+#pragma unroll 1
+        for (int b = 0; b < k; ++b) if (b != p) xs.T(t++) = (uint16_t)FID(b);
+        if (j_add >= 0) xs.T(t++) = (uint16_t)j_add;
+        const double lml_ref = score_set(P, child, xs, t, nullptr);
         const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
         if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
     }
@@ -762,7 +778,7 @@ __device__ __noinline__ int mid_move(const SspsDev& P, const int child, const St
     if (has_add && C.pev && L.n_pev < C.pev_cap)
         C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
     L.somc = (L.somc - omc_rem) + omc_add;
-    L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
+    L.ip = ip_new; L.lg_ip = lg_new;
     L.k = kn;
     if (kn <= SSPS_KS) {    // a removal that brings the set back into the SMALL tier (no arrival: kn = kr)
         #pragma unroll 1
@@ -1009,7 +1025,7 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
     const int lane = threadIdx.x & 31;
     const int V = P.V;
     const double* __restrict__ Ri = P.R + (size_t)V * child;
-    unsigned n_big = 0, n_t1 = 0;
+    unsigned n_big = 0;
     const long long t_in = clock64();
 #ifdef SSPS_PROFILE_BIG
     long long prof_[8] = {0, 0, 0, 0, 0, 0, 0, 0}; long long tp_ = clock64();
@@ -1096,10 +1112,11 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
             if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
             const double ip_new = C.yty - P.shrink * q_new;
             const float lg_new = fast_lg2((float)ip_new);
-            acc = mh_accept_ool(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, n_t1) ? 1 : 0;
+            acc = mh_accept_ool(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats) ? 1 : 0;
             if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
-                for (int b = 0; b < kn; ++b) C.xs.T(b) = (uint16_t)T.idof(b);
-                const double lml_ref = score_set(P, child, C.xs, kn, nullptr);
+                const Scratch xs = C.xs_of(lane);
+                for (int b = 0; b < kn; ++b) xs.T(b) = (uint16_t)T.idof(b);
+                const double lml_ref = score_set(P, child, xs, kn, nullptr);
                 const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
                 if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
             }
@@ -1112,7 +1129,7 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
                 if (has_add && C.pev && L.n_pev < C.pev_cap)
                     C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
                 L.somc = (L.somc - omc_rem) + omc_add;
-                L.q = q_new; L.ip = ip_new; L.lg_ip = lg_new;
+                L.ip = ip_new; L.lg_ip = lg_new;
                 L.k = kn;
                 if (kn <= SSPS_KS) L.mode = MODE_SMALL;
             }
@@ -1131,17 +1148,7 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
 #ifdef SSPS_PROFILE_BIG
     { const long long tn_ = clock64(); prof_[6] += tn_ - tp_; tp_ = tn_; }
 #endif
-    while (pend) {          // arrivals accepted by small_move with |S'| = SSPS_KS + 1
-        const int src = __ffs(pend) - 1;
-        pend &= pend - 1;
-        const int j_add = __shfl_sync(SSPS_FULL, L.pend_j, src);
-        const Stage T = C.stage(SSPS_KS + 1);
-        stage_from_small(T, S.of_lane(src - lane), SSPS_KS, lane);
-        fac_append(P, Ri, T, SSPS_KS, SSPS_NODEAD, j_add, 0.0, lane);
-        ids_append(T, SSPS_KS, j_add, rel_now, lane);
-        stage_store(T, C.big(src), SSPS_KS + 1, SSPS_NODEAD, lane);
-        if (lane == src) { L.mode = MODE_BIG; L.k = SSPS_KS + 1; }
-    }
+    (void)pend;             // arrivals into the tier are written by the arriving lane itself (small_move)
 #ifdef SSPS_PROFILE_BIG
     if (lane == 0) { prof_[7] += clock64() - tp_; for (int e_ = 0; e_ < 8; ++e_) atomicAdd(C.stats + ST_PROF + e_, (unsigned long long)prof_[e_]); }
 #endif
@@ -1149,7 +1156,6 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
         if (n_big) atomicAdd(C.stats + ST_BIG_STEPS, (unsigned long long)n_big);
         atomicAdd(C.stats + ST_BIG_CYCLES, (unsigned long long)(clock64() - t_in));
     }
-    if (n_t1) atomicAdd(C.stats + ST_TIER1, (unsigned long long)n_t1);
     return L;
 }
 
@@ -1158,7 +1164,7 @@ __device__ __noinline__ Lane task_settle(const SspsDev& P, const int child, Lane
     const int lane = threadIdx.x & 31;
     const double* __restrict__ Ri = P.R + (size_t)P.V * child;
     if (live) {
-        L.somc = sorted_somc(P, child, L.mode, S, C.big(lane), C.xs, L.k);
+        L.somc = sorted_somc(P, child, L.mode, S, C.big(lane), C.xs_of(lane), L.k);
         if (L.mode == MODE_SMALL) lane_set_q(P, child, L, small_build(P, Ri, S, L.k));
     }
     unsigned bigm = __ballot_sync(SSPS_FULL, live && L.mode == MODE_BIG);
@@ -1204,19 +1210,14 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
     }
     KCtx C;
     C.kcap = prm.kcap;
-    C.big_d0 = prm.big_d + (size_t)(gtid - lane) * SSPS_ROWLEN(prm.kcap);
-    C.big_w0 = prm.big_w + (size_t)(gtid - lane) * prm.kcap;
-    C.big_r0 = prm.big_r + (size_t)(gtid - lane) * prm.kcap;
+    C.prm = &prm; C.wbase = gtid - lane;
     C.st_smem.t = stage_smem_t; C.st_smem.tw = stage_smem_t + SSPS_TRI(SSPS_KST); C.st_smem.id = stage_smem_id; C.st_smem.rk = stage_smem_rk;
-    C.st_glob.t = prm.scr_d + (size_t)(gtid >> 5) * SSPS_ROWLEN(prm.kcap); C.st_glob.tw = C.st_glob.t + SSPS_TRI(prm.kcap);
-    C.st_glob.id = prm.scr_w + (size_t)(gtid >> 5) * prm.kcap; C.st_glob.rk = prm.scr_r + (size_t)(gtid >> 5) * prm.kcap;
-    C.xs.d = prm.x_d + gtid; C.xs.t = prm.x_t + gtid; C.xs.stride = prm.stride; C.xs.kcap = prm.kcap;
     C.stats = prm.stats; C.pev_cap = prm.pev_cap;
     const int V = P.V;
     const int thin = prm.thinning;
 
-    unsigned long long s_f3 = 0, s_midcyc = 0;
-    unsigned s_accp = 0, s_accl = 0, s_k = 0, s_b = 0, s_prop = 0, s_t1 = 0, s_lx = 0, s_mid = 0;
+    unsigned long long s_f3 = 0;
+    unsigned s_accp = 0, s_accl = 0, s_k = 0, s_b = 0, s_prop = 0;
 
     // A launch with fewer tasks than resident warps (few chains: the time-to-convergence runs) is spread over the SMs:
     // every CTA keeps only the warps its share of the tasks needs -- a warp alone on its scheduler runs a step about
@@ -1272,8 +1273,8 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
         C.yty = __ldg(P.yty + i);
         C.pev = prm.pev ? prm.pev + mc * prm.pev_cap : nullptr;
         Lane L;
-        L.k = 0; L.lam = 0.0; L.n_pev = 0; L.pend_j = -1;
-        L.q = 0.0; L.ip = 0.0; L.lg_ip = 0.f; L.somc = 0.0; L.nrmf = 0.0; L.mode = MODE_SMALL;
+        L.k = 0; L.lam = 0.0; L.n_pev = 0;
+        L.ip = 0.0; L.lg_ip = 0.f; L.somc = 0.0; L.nrmf = 0.0; L.mode = MODE_SMALL;
         if (live) {
             L.k = st.k[sidx]; L.lam = st.lambda[sidx];
             if (L.k > prm.kcap) { atomicExch(prm.stats + ST_OVERFLOW, 1ull); live = false; L.k = 0; }
@@ -1321,9 +1322,10 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
                     const double diff = SSPS_LN2 * (double)lgu - w;
                     bool acc = diff < 0.0;
                     if (!(d.u_lam > 1e-30 && fabs(diff) > (double)lmarg + 1.2e-6 * ((double)fabsf(lgu) + 1.0) + 1e-9 * fabs(w))) {
-                        ++s_lx;
-                        write_sorted(L.mode, S, C.big(lane), C.xs, L.k);
-                        acc = lambda_exact_decide(P, i, C.xs, L.k, L.lam, lam_new, d.u_lam) != 0;
+                        const Scratch xs = C.xs_of(lane);
+                        write_sorted(L.mode, S, C.big(lane), xs, L.k);
+                        acc = lambda_exact_decide(P, i, xs, L.k, L.lam, lam_new, d.u_lam) != 0;
+                        atomicAdd(prm.stats + ST_LAM_EXACT, 1ull);
                     }
                     if (acc) { L.lam = lam_new; L.nrmf = nrm_new; ++s_accl; }
                 }
@@ -1344,15 +1346,15 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
             const unsigned smallm = __ballot_sync(SSPS_FULL, live && L.mode == MODE_SMALL);
             if (live && L.mode == MODE_SMALL) {
                 int kn = 0;
-                const int acc = small_move<VERIFY>(P, i, d, mv, L, S, C, rel_now, smallm, s_t1, kn);
+                const int acc = small_move<VERIFY>(P, i, d, mv, L, S, C, rel_now, smallm, kn);
                 acc_kn = acc | (kn << 1);
             }
             unsigned midm = __ballot_sync(SSPS_FULL, is_mid);
             while (midm) {      // rounds of SSPS_MID_SLOTS lanes: the warp copies their factors into Stage slots, each lane moves its own
-                const long long t_mid = clock64();
                 const int my_slot = __popc(midm & ((1u << lane) - 1u));
                 const bool mine = is_mid && ((midm >> lane) & 1u) && my_slot < SSPS_MID_SLOTS;
                 const unsigned round = __ballot_sync(SSPS_FULL, mine);
+                if (lane == 0) atomicAdd(prm.stats + ST_MID_STEPS, (unsigned long long)__popc(round));
                 unsigned rm = round;
                 double* Fs = C.st_smem.t;
                 while (rm) {
@@ -1372,9 +1374,8 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
                 __syncwarp();
                 if (mine) {
                     int kn = 0;
-                    const int acc = mid_move<VERIFY>(P, i, d, mv, L, S, C.big(lane), C.st_smem.t + my_slot * SSPS_MID_SLOT, C, rel_now, s_t1, kn);
+                    const int acc = mid_move<VERIFY>(P, i, d, mv, L, S, C.big(lane), C.st_smem.t + my_slot * SSPS_MID_SLOT, C, rel_now, kn);
                     acc_kn = acc | (kn << 1);
-                    ++s_mid; s_midcyc += (unsigned long long)(clock64() - t_mid);
                 }
                 __syncwarp();
                 midm &= ~round;
@@ -1385,7 +1386,6 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
             if (live) {
                 const int kn = acc_kn >> 1;
                 s_accp += (unsigned)(acc_kn & 1);
-                ++s_prop;
                 s_k += (unsigned)kn;
                 s_f3 += (unsigned long long)((unsigned)kn * ((unsigned)kn * ((unsigned)kn + 6u) + 6u));   // k^3 + 6 k^2 + 6 k < 2^32 for k <= 1600
                 s_b += (unsigned)(kn * (kn + 1) / 2 + kn);
@@ -1408,6 +1408,7 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
 
         // flush lazy tallies, store the parent list (arrival order, id | rank << 16) and the state
         if (live) {
+            s_prop += (unsigned)prm.n_local;
             const int rec_local = prm.n_local / thin;
             const BigRef B = C.big(lane);
             for (int b = 0; b < L.k; ++b) {
@@ -1429,10 +1430,10 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
     }
 
     // stats: warp reduce, one atomic per warp
-    unsigned long long v[10] = {s_accp, s_accl, s_k, s_f3, s_b, s_prop, s_t1, s_lx, s_mid, s_midcyc};
-    const int slot[10] = {ST_ACCP, ST_ACCL, ST_SUMK, ST_F3, ST_BYTES, ST_PROP, ST_TIER1, ST_LAM_EXACT, ST_MID_STEPS, ST_MID_CYCLES};
+    unsigned long long v[6] = {s_accp, s_accl, s_k, s_f3, s_b, s_prop};
+    const int slot[6] = {ST_ACCP, ST_ACCL, ST_SUMK, ST_F3, ST_BYTES, ST_PROP};
 #pragma unroll 1
-    for (int e = 0; e < 10; ++e) {
+    for (int e = 0; e < 6; ++e) {
         unsigned long long x = v[e];
         for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(SSPS_FULL, x, o);
         if (lane == 0 && x) atomicAdd(prm.stats + slot[e], x);

@@ -28,7 +28,7 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
               (st.big_cycles - prev.big_cycles) / max(float(s.vertex_cost()[0].sum()) * 4, 1.0)))
         prev = st
         r = s.raw_stats(32)
-        print("      mid: %d lane-steps (%.2e per proposal), %.0f cycles per mid lane-step (cumulative)" % (r[14], r[14] / max(st.n_proposals, 1), r[15] / max(r[14], 1)))
+        print("      mid: %d lane-steps (%.2e per proposal), (cumulative)" % (r[14], r[14] / max(st.n_proposals, 1)))
     cost, mk, sp = s.vertex_cost()
     n_slabs = (C + 31) // 32
     task = cost / (n_slabs * sp)

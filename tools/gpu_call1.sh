@@ -1,11 +1,6 @@
 #!/bin/bash
-# round-end style check: GPU tests, smoke, default bench, launch list, one full ncu capture of the MH kernel
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_gpu.log
 tail -3 gpurun_out/pytest_gpu.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
-timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"; cat gpurun_out/bench.json
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-psrf > gpurun_out/ncu_l.log 2>&1; echo "launch list exit $?"
-timeout 600 ncu --set full --import-source on --clock-control none -k regex:mh_sweeps -s 8 -c 1 -f -o gpurun_out/r1j_mh \
-   python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-psrf > gpurun_out/ncu_r1j.log 2>&1; echo "ncu exit $?"
+for i in 1 2 3 4 5 6; do SSPS_TRACE=1 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-psrf 2>gpurun_out/tr$i.err | python -c "import sys,json; d=json.loads(sys.stdin.readline()); print('%.3e'%d['value'], d['ms_per_step'], 'e2e %.3e'%d['e2e']['value'])"; grep trace gpurun_out/tr$i.err | head -5; done
