@@ -938,32 +938,31 @@ __device__ __noinline__ double fac_remove(const SspsDev& P, const double* __rest
         ra[SCOL(c)] = x;
     }
     __syncwarp();
+    // Trailing update, a lane per row (rows a = p + lane, + 32, ...): once column b is final, lane a scales its entry of
+    // that column and subtracts its products from the entries (a, c), b < c <= a, of its own row.  Every entry still
+    // receives its terms in ascending b through fma -- the bits of the row-by-row factorisation.  (The pair-per-lane
+    // form of the first version spent more on decoding pair numbers than on the fma they led to.)
+    double gd = 0.0;                                    // G_aa of this lane's first row: the pivots' tolerance reference
+    if (p + lane < kr) { const int ja = T.idof(p + lane); gd = __ldg(P.G + (size_t)ja * V + ja); }
     for (int b = p; b < kr; ++b) {
-        const int jb = T.idof(b);
-        const double gbb = __ldg(P.G + (size_t)jb * V + jb);
         double* rb = SROW(b);
         const double d2 = rb[SCOL(b)], tb = tw[b + 1];
+        double gbb = __shfl_sync(SSPS_FULL, gd, (b - p) & 31);
+        if (b - p >= 32) { const int jb = T.idof(b); gbb = __ldg(P.G + (size_t)jb * V + jb); }
         double inv, wb;
         chol_pivot(d2, gbb, tb, inv, wb, q);
         __syncwarp();                               // every lane has read d2 and t_b
         if (lane == 0) { rb[SCOL(b)] = inv; tw[b + 1] = wb; }
-        const int nr = kr - 1 - b;                  // rows below b
-        for (int idx = lane; idx < nr * (nr + 1) / 2; idx += 32) {
-            int u, v;
-            tri_decode(idx, u, v);
-            const int a = kr - 1 - u, c = kr - 1 - v;
-            double* ra = SROW(a);
-            const double lab = ra[SCOL(b)] * inv;
-            if (c == a) {
-                ra[SCOL(a)] = fma(-lab, lab, ra[SCOL(a)]);
-                tw[a + 1] = fma(-lab, wb, tw[a + 1]);
-            } else {
-                const double lcb = SROW(c)[SCOL(b)] * inv;
-                ra[SCOL(c)] = fma(-lab, lcb, ra[SCOL(c)]);
-            }
-        }
-        __syncwarp();                               // column b has been read by everyone: scale it in place
         for (int a = b + 1 + lane; a < kr; a += 32) { double* ra = SROW(a); ra[SCOL(b)] = ra[SCOL(b)] * inv; }
+        __syncwarp();                               // column b is final
+        for (int a = b + 1 + lane; a < kr; a += 32) {
+            double* ra = SROW(a);
+            const double lab = ra[SCOL(b)];
+            for (int c = b + 1; c < a; ++c) ra[SCOL(c)] = fma(-lab, SROW(c)[SCOL(b)], ra[SCOL(c)]);
+            ra[SCOL(a)] = fma(-lab, lab, ra[SCOL(a)]);
+            tw[a + 1] = fma(-lab, wb, tw[a + 1]);
+        }
+        __syncwarp();
     }
     __syncwarp();
 #undef SROW
@@ -973,17 +972,18 @@ __device__ __noinline__ double fac_remove(const SspsDev& P, const double* __rest
 
 // Row kr of the proposed set's factor: parent j appended to its kr rows (forward substitution, lane owns
 // columns lane + 32 u).  pd = dead stage row / column (SSPS_NODEAD: none).  Returns q + w_kr^2.
-__device__ __noinline__ double fac_append(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int kr, const int pd,
-                                          const int j, double q, const int lane) {
+template <int KU>
+__device__ __noinline__ double fac_append_ku(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int kr, const int pd,
+                                             const int j, double q, const int lane) {
     const int V = P.V;
     double* t = T.t; double* tw = T.tw;
     const double* __restrict__ Gj = P.G + (size_t)j * V;
     const double gjj = __ldg(Gj + j);
     double d2 = gjj, tj = __ldg(Ri + j);
-    double sc[SSPS_KU];
-    const double* myrow[SSPS_KU];
+    double sc[KU];
+    const double* myrow[KU];
 #pragma unroll
-    for (int u = 0; u < SSPS_KU; ++u) {
+    for (int u = 0; u < KU; ++u) {
         const int c = lane + 32 * u;
         sc[u] = (c < kr) ? __ldg(Gj + T.idof(c)) : 0.0;
         myrow[u] = t + SSPS_TRI(st_map(c < kr ? c : 0, pd));
@@ -994,14 +994,16 @@ __device__ __noinline__ double fac_append(const SspsDev& P, const double* __rest
         const double invb = t[SSPS_TRI(sb) + sb];
         const double wb = tw[sb];
         double mine = sc[0];
+        if (KU > 1) {
 #pragma unroll
-        for (int u = 1; u < SSPS_KU; ++u) if ((b >> 5) == u) mine = sc[u];
+            for (int u = 1; u < KU; ++u) if ((b >> 5) == u) mine = sc[u];
+        }
         const double l = __shfl_sync(SSPS_FULL, mine * invb, b & 31);
         d2 = fma(-l, l, d2);
         tj = fma(-l, wb, tj);
         if (lane == (b & 31)) rj[sb] = l;
 #pragma unroll
-        for (int u = 0; u < SSPS_KU; ++u) {
+        for (int u = 0; u < KU; ++u) {
             const int c = lane + 32 * u;
             if (c > b && c < kr) sc[u] = fma(-l, myrow[u][sb], sc[u]);
         }
@@ -1011,6 +1013,12 @@ __device__ __noinline__ double fac_append(const SspsDev& P, const double* __rest
     if (lane == 0) { rj[st_map(kr, pd)] = inv; tw[st_map(kr, pd)] = wj; }
     __syncwarp();
     return q;
+}
+
+// up to 32 rows: a lane owns one column, a quarter of the code per step (the common case by far)
+__device__ __forceinline__ double fac_append(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int kr, const int pd,
+                                             const int j, double q, const int lane) {
+    return kr <= 32 ? fac_append_ku<1>(P, Ri, T, kr, pd, j, q, lane) : fac_append_ku<SSPS_KU>(P, Ri, T, kr, pd, j, q, lane);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1488,6 +1496,9 @@ __global__ void __launch_bounds__(256) schedule_kernel(const unsigned long long*
     }
     atomicAdd(&sh_sum, lsum);
     __syncthreads();
+    // a launch with far fewer tasks than resident warps (few chains: time-to-convergence runs) lasts as long as its longest
+    // task: the tail gets full weight there, so that every heavy slab is spread until that stops shortening it
+    const double tail_w = (2 * (long long)V * n_slabs <= (long long)n_warps) ? 1.0 : SSPS_TAIL_WEIGHT;
     if (model) {
         double load = sh_sum * (double)n_slabs / (double)n_warps;      // all task cycles / resident warps
         for (int it = 0; it < 5 * V; ++it) {
@@ -1504,11 +1515,11 @@ __global__ void __launch_bounds__(256) schedule_kernel(const unsigned long long*
                 for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
                     if (sh_val[w] > bv || (sh_val[w] == bv && sh_idx[w] >= 0 && (bi < 0 || sh_idx[w] < bi))) { bv = sh_val[w]; bi = sh_idx[w]; }
                 const int sp = split[bi];
-                const double cur = SSPS_TAIL_WEIGHT * bv + load;
+                const double cur = tail_w * bv + load;
                 const double e_new = base + big[bi] / (double)(2 * sp);
                 const double load_new = load + (double)n_slabs * (double)sp * base / (double)n_warps;   // sp more tasks, each + base
                 // the runner-up is not known here; e_new bounds the new longest task from below, which is enough to reject
-                if (sp >= SSPS_MAX_SPLIT || big[bi] <= 0.0 || SSPS_TAIL_WEIGHT * e_new + load_new >= cur) sh_stop = 1;
+                if (sp >= SSPS_MAX_SPLIT || big[bi] <= 0.0 || tail_w * e_new + load_new >= cur) sh_stop = 1;
                 else { split[bi] = 2 * sp; est[bi] = e_new; sh_sum = load_new; }
             }
             __syncthreads();
