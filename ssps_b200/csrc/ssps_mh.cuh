@@ -37,7 +37,7 @@
 #include "ssps_kernels.cuh"
 
 #ifndef SSPS_KS
-#define SSPS_KS 6
+#define SSPS_KS 5
 #endif
 #ifndef SSPS_LOCKSTEP
 #define SSPS_LOCKSTEP 1      // 1: the warps of a scheduler walk the sweep in step (named barrier per sweep); 2: the whole CTA; 0: off
@@ -1241,7 +1241,7 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
     const int LS_N = min(SSPS_BLOCK / 32, warps_needed);
 #else
     const int ls_sched = (threadIdx.x >> 5) & 3, ls_member = threadIdx.x >> 7;
-    const int LS_N = min(SSPS_BLOCK / 128, (warps_needed + 3) / 4);
+    const int LS_N = min((SSPS_BLOCK / 32 - ls_sched + 3) / 4, (warps_needed + 3) / 4);     // warps on this scheduler (block sizes that are not a multiple of 128 too)
 #endif
     if (ls_member >= LS_N) return;
 #define LS_BAR() asm volatile("bar.sync %0, %1;" ::"r"(1 + ls_sched), "r"(32 * LS_N) : "memory")
