@@ -107,7 +107,7 @@ def run_reference(args, rank, world):
         tot_p += nprop
     value = tot_p / tot_t
     sample = "%d chains x %d sweeps per step on %d threads (oracle QR scorer + [i;S] lml cache)" % (chains, sweeps, cores)
-    print(json.dumps({
+    emit_line(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -394,10 +394,32 @@ def run_ours(args, rank, world, local_rank):
     }
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args)
-    print(json.dumps(out))
+    emit_line(json.dumps(out))
+
+
+_REAL_STDOUT = None
+
+
+def protect_stdout():
+    """stdout must hold ONE JSON line: libraries (NCCL's version banner, whatever NCCL_DEBUG says) write to fd 1 directly,
+    so fd 1 is pointed at stderr for the run and the line goes to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        print(line, flush=True)
+    else:
+        os.write(_REAL_STDOUT, (line + "\n").encode())
 
 
 def main():
+    protect_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
