@@ -272,8 +272,12 @@ def test_cached_factor_scores_are_from_scratch_scores(which, c1):
         s.generate(nch, seed=9)
         s.update_loop(nsw)
         st = s.stats()
+        raw = s.raw_stats(32)
     assert st.n_proposals == nch * xm.shape[1] * nsw
     assert st.n_mismatch == 0
+    if which == "c1":       # every storage tier took part: lane-owned MID moves (slot 14) and warp-cooperative BIG passes
+        assert raw[14] > 0 and st.n_big_steps > 0, (int(raw[14]), st.n_big_steps)
+        assert raw[14] + st.n_big_steps < st.n_proposals
     assert st.n_tier1 < 1e-3 * st.n_proposals and st.n_lambda_exact < 1e-2 * st.n_proposals
 
 
