@@ -683,6 +683,12 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
 #ifndef SSPS_KM
 #define SSPS_KM 16
 #endif
+#ifndef SSPS_MID_UNROLL
+#define SSPS_MID_UNROLL 1    // inner loops of mid_move: 1 = smallest code (what a rarely visited path pays for)
+#endif
+#define SSPS_PRAGMA_(x) _Pragma(#x)
+#define SSPS_PRAGMA(x) SSPS_PRAGMA_(x)
+#define SSPS_UNROLL_MID SSPS_PRAGMA(unroll SSPS_MID_UNROLL)
 #define SSPS_MID_SLOT (SSPS_ROWLEN(SSPS_KM) + SSPS_KM)            // doubles: factor, w, then ids (words) and ranks (halves)
 #define SSPS_MID_SLOTS (SSPS_ROWLEN(SSPS_KST) / SSPS_MID_SLOT)
 template <bool VERIFY>
@@ -735,15 +741,15 @@ __device__ __noinline__ int mid_move(const SspsDev& P, const int child, const St
         double d2 = gaa, t = __ldg(Ri + ja);
         const double* olda = F + SSPS_TRI(a + 1);
         double* xa = F + SSPS_TRI(a);
-#pragma unroll 1
+SSPS_UNROLL_MID
         for (int b = 0; b < c0; ++b) { const double l = olda[b]; xa[b] = l; d2 = fma(-l, l, d2); t = fma(-l, Fw[b], t); }
-#pragma unroll 1
+SSPS_UNROLL_MID
         for (int b = c0; b < a; ++b) xa[b] = __ldg(Ga + FID(b + (b >= p ? 1 : 0)));     // the gathers first, back to back: what follows is a dependent chain
 #pragma unroll 1
         for (int b = c0; b < a; ++b) {
             const double* xb = F + SSPS_TRI(b);
             double s = xa[b];
-#pragma unroll 1
+SSPS_UNROLL_MID
             for (int m = 0; m < b; ++m) s = fma(-xa[m], xb[m], s);
             const double l = s * xb[b];
             xa[b] = l; d2 = fma(-l, l, d2); t = fma(-l, Fw[b], t);
