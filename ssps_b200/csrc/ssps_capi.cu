@@ -939,7 +939,8 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
     CK(cudaStreamSynchronize(h->stream));
     if (getenv("SSPS_TRACE")) {
         const double ms = 1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-        float kms = 0; for (size_t e = 0; e < ev_used; ++e) { float m1 = 0; cudaEventElapsedTime(&m1, h->ev_pool[e].first, h->ev_pool[e].second); kms += m1; }
+        float kms = 0; for (size_t e = 0; e < ev_used; ++e) { float m1 = 0; cudaEventElapsedTime(&m1, h->ev_pool[e].first, h->ev_pool[e].second); kms += m1;
+            if (atoi(getenv("SSPS_TRACE")) >= 2) fprintf(stderr, "[ssps trace] launch %zu: %.2f ms\n", e, m1); }
         if (ms > 1.5 * kms + 2.0) fprintf(stderr, "[ssps trace] run_sweeps %.1f ms wall, %.1f ms in the MH kernel (%lld sweeps)\n", ms, kms, (long long)done);
     }
     for (size_t e = 0; e < ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
