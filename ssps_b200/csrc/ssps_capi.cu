@@ -576,6 +576,7 @@ void chain_chunks(const ssps_handle* h, size_t vv, int& chunks, int& chunk_len) 
     const size_t want = (size_t)h->sm_count * 2048;
     chunks = (int)std::max<size_t>(1, std::min<size_t>((want + vv - 1) / vv, (size_t)std::max(1, h->n_chains / 32)));
     chunks = std::min(chunks, 64);
+    if (const char* e = getenv("SSPS_K4_CHUNKS")) chunks = std::max(1, std::min(atoi(e), h->n_chains));     // test hook
     chunk_len = (h->n_chains + chunks - 1) / chunks;
     chunks = (h->n_chains + chunk_len - 1) / chunk_len;
 }

@@ -360,6 +360,37 @@ def test_psrf_and_posterior_vs_oracle(c1, c1_problem, oracle):
     assert mx == pytest.approx(worst, rel=1e-9)
 
 
+@pytest.mark.gpu
+def test_k4_chain_chunking_is_exact_and_order_stable(monkeypatch):
+    """K4 splits the chains over gridDim.y chunks: the pooled posterior (integer tallies) must not depend on the
+    chunk count at all, the PSRF only in the last bits (chunk partials are added in ascending order), and both must
+    equal what numpy derives from the per-chain tallies."""
+    from ssps_b200 import Sampler
+    ds, xm, xp = make_synth(40, seed=20200702)
+    res = {}
+    for chunks in ("1", "3", "7"):
+        monkeypatch.setenv("SSPS_K4_CHUNKS", chunks)
+        with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=50) as s:
+            s.set_data(xm, xp, ds.prior_graph)
+            s.generate(96, seed=5)
+            s.update_loop(200)
+            mx, edge = s.psrf(0.5)
+            probs, lam_mean, _, _ = s.edge_posterior(0.0)
+            counts, n_samples, _ = s.edge_counts()
+            res[chunks] = (mx, edge.copy(), probs.copy(), lam_mean.copy(), counts.copy(), n_samples)
+    ref = res["1"]
+    for chunks in ("3", "7"):
+        mx, edge, probs, lam_mean, counts, n = res[chunks]
+        assert np.array_equal(counts, ref[4]) and n == ref[5]
+        assert np.array_equal(probs, ref[2])
+        np.testing.assert_allclose(lam_mean, ref[3], rtol=1e-13)
+        fin = np.isfinite(ref[1])
+        assert np.array_equal(np.isfinite(edge), fin)
+        np.testing.assert_allclose(edge[fin], ref[1][fin], rtol=1e-12)
+        assert abs(mx - ref[0]) <= 1e-12 * abs(ref[0])
+    np.testing.assert_allclose(ref[2], ref[4] / (96.0 * ref[5]), rtol=1e-15)
+
+
 def test_full_size_properties_metric_point():
     """Size-independent properties at the bench workload (V=100, n=28): tallies are consistent
     with the sample count, the swap move preserves in-degree bookkeeping, stats add up."""
