@@ -466,6 +466,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
         if (b < k) { idw[b] = S.W(b); rk[b] = S.rank(b); }
     }
     int j_add = -1, j_rem = -1, p = k, rp = 1 << 20;
+    uint32_t w_rem = 0;
     if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
         int c = 0;
 #pragma unroll
@@ -475,7 +476,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     if (has_rem) {          // the r-th element of the sorted list
         rp = r_ord - 1;
 #pragma unroll
-        for (int b = 0; b < KS; ++b) if (rk[b] == rp) { p = b; j_rem = (int)(idw[b] & 0xffffu); }
+        for (int b = 0; b < KS; ++b) if (rk[b] == rp) { p = b; w_rem = idw[b]; j_rem = (int)(w_rem & 0xffffu); }      // (no dynamic index: idw stays in registers)
     }
     const int kr = k - (has_rem ? 1 : 0);
     const int kn = kr + (has_add ? 1 : 0);
@@ -612,7 +613,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
 
     // ---- accepted: tallies / change points ----
     if (has_rem) {
-        const int credit = rel_now - (int)(idw[(p < KS) ? p : 0] >> 16);
+        const int credit = rel_now - (int)(w_rem >> 16);
         if (credit > 0) atomicAdd(C.cnt_row + j_rem, (uint32_t)credit);     // RED: the lane owns the counter, nothing waits for the old value
         if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
     }
@@ -644,8 +645,9 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     for (int a = 0; a < KS; ++a) {
         if (a < kr) {
             // slot a of the reduced set = old slot a (a < p) or a + 1
-            const uint32_t w_old = (a >= p && a + 1 < KS) ? idw[(a + 1 < KS) ? a + 1 : a] : idw[a];
-            int r_old = (a >= p && a + 1 < KS) ? rk[(a + 1 < KS) ? a + 1 : a] : rk[a];
+            // (read back from shared memory rather than held in registers across the factor work; slot a + 1 is still the old one)
+            const uint32_t w_old = (a >= p && a + 1 < KS) ? S.W((a + 1 < KS) ? a + 1 : a) : S.W(a);
+            int r_old = (a >= p && a + 1 < KS) ? S.rank((a + 1 < KS) ? a + 1 : a) : S.rank(a);
             r_old -= (r_old > rp) ? 1 : 0;
             if (has_add) { if ((int)(w_old & 0xffffu) < j_add) ++rj; else ++r_old; }
             if (a >= p) {
