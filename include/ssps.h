@@ -205,6 +205,10 @@ int  ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles /* V */, int32_t* mean
 /* Device-side microbenchmark used by bench.py for the FP64 roofline denominator: dependent-free
  * DFMA streams on every SM; returns achieved TFLOP/s. */
 int  ssps_measure_fp64_peak(ssps_handle* h, double* tflops);
+/* Device blocks released by destroyed handles are kept in a process-wide cache for the next handle of the same
+ * shapes (cudaMalloc of the 100 MB-class buffers costs 2..100 ms).  This returns the cached blocks of `device` to the
+ * driver; live handles are not affected.  No counterpart in the reference (Julia's GC owns its memory). */
+int  ssps_release_cached_memory(int32_t device);
 
 #ifdef __cplusplus
 }

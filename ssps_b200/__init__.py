@@ -13,6 +13,6 @@ Layout (only what the path needs):
 Importing the package never touches oracle/ (test infrastructure) and has no CPU fallback.
 """
 from ._lib import SspsError, load, lib_path  # noqa: F401
-from .sampler import Sampler  # noqa: F401
+from .sampler import Sampler, release_cached_memory  # noqa: F401
 
-__all__ = ["Sampler", "SspsError", "load", "lib_path"]
+__all__ = ["Sampler", "SspsError", "load", "lib_path", "release_cached_memory"]

@@ -1367,6 +1367,16 @@ int ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles, int32_t* mean_indeg_x1
     return SSPS_OK;
 }
 
+int ssps_release_cached_memory(int32_t device) {
+    int prev = 0;
+    CK(cudaGetDevice(&prev));
+    CK(cudaSetDevice(device));
+    CK(cudaDeviceSynchronize());
+    BlockCache::get().trim(device);
+    CK(cudaSetDevice(prev));
+    return SSPS_OK;
+}
+
 int ssps_measure_fp64_peak(ssps_handle* h, double* tflops) {
     CKS(bind(h));
     if (!tflops) return fail(SSPS_ERR_INVALID, "null out");

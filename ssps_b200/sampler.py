@@ -57,6 +57,11 @@ def sets_to_csr(sets: Sequence[Sequence[int]]):
     return offs, mem
 
 
+def release_cached_memory(device: int = 0) -> None:
+    """ssps_release_cached_memory: hand the device blocks kept from destroyed handles back to the driver."""
+    check(_lib.load().ssps_release_cached_memory(int(device)))
+
+
 class Sampler:
     """One GPU's worth of SSPS chains behind libssps_b200.so."""
 

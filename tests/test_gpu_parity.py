@@ -361,6 +361,28 @@ def test_psrf_and_posterior_vs_oracle(c1, c1_problem, oracle):
 
 
 @pytest.mark.gpu
+def test_block_cache_release_and_reuse(c1):
+    """Device blocks of a destroyed handle are recycled; ssps_release_cached_memory returns them to the driver and the
+    next handle still works and reproduces the same chain."""
+    import torch
+    from ssps_b200 import Sampler, release_cached_memory
+    out = []
+    for rep in range(3):
+        with Sampler(large_indeg=20.0, lambda_prop_std=3.0, psrf_grid=50) as s:
+            s.set_data(c1["Xminus"], c1["Xplus"], c1["prior"])
+            s.generate(64, seed=3)
+            s.update_loop(100)
+            sets, lam, _ = s.state(5)
+            out.append((sets, lam.copy()))
+        if rep == 1:
+            free0 = torch.cuda.mem_get_info(0)[0]
+            release_cached_memory(0)
+            assert torch.cuda.mem_get_info(0)[0] >= free0
+    assert out[0][0] == out[1][0] == out[2][0]
+    assert np.array_equal(out[0][1], out[1][1]) and np.array_equal(out[0][1], out[2][1])
+
+
+@pytest.mark.gpu
 def test_k4_chain_chunking_is_exact_and_order_stable(monkeypatch):
     """K4 splits the chains over gridDim.y chunks: the pooled posterior (integer tallies) must not depend on the
     chunk count at all, the PSRF only in the last bits (chunk partials are added in ascending order), and both must
