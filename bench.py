@@ -191,14 +191,14 @@ def time_to_psrf_cpu(args):
             "what": "oracle (QR scorer + lml cache), one chain per core, tallies snapshotted every %d sweeps" % g}
 
 
-def time_to_psrf_gpu(args, rank, world, local_rank, stream, dev):
+def time_to_psrf_gpu(args, rank, world, local_rank, stream, dev, chains_per_gpu=None, what=None):
     """M2 on the device: wall time (host clock, everything included: set_data, init, sweeps, PSRF reductions) until the max
     edge split-PSRF over ALL ranks' chains drops below the threshold, checked every `psrf_check` sweeps."""
     import torch
     import torch.distributed as dist
     from ssps_b200 import Sampler
     ds, xm, xp = make_workload(args.V, args.T, args.M)
-    C = args.psrf_chains
+    C = chains_per_gpu or args.psrf_chains
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -232,7 +232,8 @@ def time_to_psrf_gpu(args, rank, world, local_rank, stream, dev):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     return {"threshold": args.psrf_threshold, "reached": bool(reached), "seconds": float(tt.item()), "sweeps": done,
             "chains": C * world, "max_edge_psrf": psrf, "check_every": args.psrf_check,
-            "what": "%d chains per GPU (few chains: the scheduler gives heavy micro-chains a warp of their own, so a sweep costs one step latency); "
+            "what": (what + "; " if what else "") +
+                    "%d chains per GPU (few chains: the scheduler gives heavy micro-chains a warp of their own, so a sweep costs one step latency); "
                     "wall clock incl. set_data, init and the PSRF reductions" % C}
 
 
@@ -377,7 +378,14 @@ def run_ours(args, rank, world, local_rank):
                "what": "per step: ssps_create + set_data(H2D) + init_chains + %d sweeps + psrf + edge_posterior(D2H), wall clock" % S}
 
     smp.close()
-    ttp = None if args.no_psrf else time_to_psrf_gpu(args, rank, world, local_rank, stream, dev)
+    # M2 twice: the SAME job as the reference arm times (one chain per host core of this box, sharded over the GPUs), and a many-chain
+    # run (--psrf-chains per GPU): time to convergence is sequential, so more chains only add the slowest micro-chain's tail
+    ttp = ttp_many = None
+    if not args.no_psrf:
+        cores = os.cpu_count() or 1
+        ttp = time_to_psrf_gpu(args, rank, world, local_rank, stream, dev, chains_per_gpu=max(1, -(-cores // world)),
+                               what="same job as the reference arm: %d chains = one per host core" % cores)
+        ttp_many = time_to_psrf_gpu(args, rank, world, local_rank, stream, dev)
     if rank != 0:
         return
     out = {
@@ -391,7 +399,7 @@ def run_ours(args, rank, world, local_rank):
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(st1.kernel_launches - st0.kernel_launches),
         "clocks": clk.summary(), "max_edge_psrf": max_psrf,
         "accept_rate": float(agg[1].item()) / max(proposals, 1.0),
-        "time_to_psrf": ttp,
+        "time_to_psrf": ttp, "time_to_psrf_many_chains": ttp_many,
     }
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args)
