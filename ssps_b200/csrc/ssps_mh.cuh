@@ -1467,12 +1467,12 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
 //   start[rank]    first task id of that vertex; start[V] = number of tasks
 // Model: a task of v at split s costs  base + big_v / s  (base = a task without BIG lanes); the launch
 // takes about  all task cycles / resident warps + SSPS_TAIL_WEIGHT x longest task  (list scheduling, longest
-// first: the bound has weight 1, a full grid hides most of the tail: 0.1 measured best).  Greedy: keep halving the lanes of the
+// first: the bound has weight 1, a full grid hides most of the tail: see SSPS_TAIL_WEIGHT).  Greedy: keep halving the lanes of the
 // longest task while that lowers this estimate.  One CTA; V is at most a few thousand.
 // ------------------------------------------------------------------------------------------------
 #define SSPS_MAX_SPLIT 32
 #ifndef SSPS_TAIL_WEIGHT
-#define SSPS_TAIL_WEIGHT 0.1
+#define SSPS_TAIL_WEIGHT 0.045     // measured plateau 0.035 .. 0.06 with the MID tier (6.1e9 proposals/s; 0.02 and 0.1 give 5.6e9)
 #endif
 __global__ void __launch_bounds__(256) schedule_kernel(const unsigned long long* __restrict__ cost, int V, int n_slabs, int n_warps,
                                                        int have_cycles, int* __restrict__ split /* in: previous, out: this launch */,
