@@ -277,6 +277,7 @@ def run_ours(args, rank, world, local_rank):
     except Exception:
         pass
     st0 = smp.stats()
+    raw_before = smp.raw_stats()
     barrier()
     clk = ClockSampler(local_rank)
     clk.start()
@@ -315,6 +316,11 @@ def run_ours(args, rank, world, local_rank):
             traffic = ncu["dram_bytes_per_launch"]
     except Exception:
         ncu = None
+    raw0, raw1 = raw_before, smp.raw_stats()
+    big_steps, mid_steps = int(raw1[13] - raw0[13]), int(raw1[14] - raw0[14])
+    tier_mix = {"small": 1.0 - (big_steps + mid_steps) / max(nprop_local, 1), "mid": mid_steps / max(nprop_local, 1),
+                "big": big_steps / max(nprop_local, 1),
+                "what": "share of the timed proposals scored in each storage tier (|S| <= 5 registers+smem, 6..15 lane-owned Stage, >= 16 warp-cooperative)"}
     roofline = {"bound": "fp64", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": traffic,
                 "kernel": "mh_sweeps_kernel<PhiloxSource>", "launches": launches, "avg_launch_ms": k_ms / max(launches, 1),
                 "kernel_share_of_step": k_ms / ms,
@@ -361,11 +367,18 @@ def run_ours(args, rank, world, local_rank):
                       % tuple(1e3 * (tp[e + 1] - tp[e]) for e in range(6)), file=sys.stderr)
             return probs
 
+        from ssps_b200.sampler import release_cached_memory
+        release_cached_memory(local_rank)       # the first step below is COLD: every device block comes from cudaMalloc
+        barrier()
+        tc = time.perf_counter()
+        e2e_step(1000)
+        barrier()
+        cold_s = time.perf_counter() - tc
         for w in range(min(args.warmup, 2)):
-            e2e_step(1000 + w)
+            e2e_step(1001 + w)
         barrier()
         t0 = time.perf_counter()
-        n_e2e = max(1, min(args.steps, 3))
+        n_e2e = max(10, args.steps) if not args.e2e_steps else args.e2e_steps
         for k in range(n_e2e):
             e2e_step(2000 + k)
         barrier()
@@ -375,7 +388,10 @@ def run_ours(args, rank, world, local_rank):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e = {"value": world * C * V * S * n_e2e / float(tt.item()), "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "steps": n_e2e,
-               "what": "per step: ssps_create + set_data(H2D) + init_chains + %d sweeps + psrf + edge_posterior(D2H), wall clock" % S}
+               "cold_first_step": {"value": world * C * V * S / cold_s, "seconds": cold_s,
+                                   "what": "the same step on an empty block cache (all device memory from cudaMalloc), not in `value`"},
+               "what": "per step: ssps_create + set_data(H2D) + init_chains + %d sweeps + psrf + edge_posterior(D2H), wall clock; steady state: "
+                       "a new handle per step re-uses the device blocks of the previous one through the library's block cache" % S}
 
     smp.close()
     # M2 twice: the SAME job as the reference arm times (one chain per host core of this box, sharded over the GPUs), and a many-chain
@@ -397,6 +413,9 @@ def run_ours(args, rank, world, local_rank):
                    "chains_per_gpu": C, "sweeps_per_step": S, "parallelism": "chains sharded over %d GPU(s), no data-path collective; one PSRF all-reduce per timed region" % world,
                    "l2": "chain state + tallies (%.0f MB) exceed L2; G/R tables (%.0f kB) are cache-resident by design" % (2 * C * V * V * 4 / 1e6, 2 * V * V * 8 / 1e3)},
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(st1.kernel_launches - st0.kernel_launches),
+        "sweeps_before_timed_region": int(st0.sweeps_done), "tier_mix": tier_mix,
+        "device_allocs_in_timed_region": int(st1.device_allocs_in_run - st0.device_allocs_in_run),
+        "snapshots": {"slots": int(st1.snapshot_slots), "live": int(st1.snapshots_live), "grid": int(st1.snapshot_grid)},
         "clocks": clk.summary(), "max_edge_psrf": max_psrf,
         "accept_rate": float(agg[1].item()) / max(proposals, 1.0),
         "time_to_psrf": ttp, "time_to_psrf_many_chains": ttp_many,
@@ -459,6 +478,7 @@ def main():
     ap.add_argument("--large-indeg", type=float, default=15.0)
     ap.add_argument("--lambda-prop-std", type=float, default=3.0)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="timed end-to-end steps (default: max(10, --steps))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-psrf", action="store_true", help="skip the wall-time-to-PSRF<threshold measurement (metric M2)")
     ap.add_argument("--psrf-chains", type=int, default=128, help="chains per GPU for M2 (few: every micro-chain gets its own warp)")

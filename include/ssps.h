@@ -51,7 +51,7 @@
 extern "C" {
 #endif
 
-#define SSPS_ABI_VERSION 2
+#define SSPS_ABI_VERSION 3
 
 typedef enum {
     SSPS_OK = 0,
@@ -59,7 +59,8 @@ typedef enum {
     SSPS_ERR_CUDA = -2,         /* CUDA runtime error (message has the cudaError string) */
     SSPS_ERR_UNSUPPORTED = -3,  /* e.g. a set too large for the interaction-column path, --proposal uniform */
     SSPS_ERR_NOMEM = -4,
-    SSPS_ERR_INDEGREE = -5,     /* a proposed parent set exceeded max_indegree scratch */
+    SSPS_ERR_INDEGREE = -5,     /* an INITIAL parent set exceeds max_indegree (ssps_init_chains); proposals beyond the bound
+                                   are rejected, not errors */
     SSPS_ERR_UNAVAILABLE = -6   /* e.g. PSRF requested before any snapshot exists */
 } ssps_status;
 
@@ -72,8 +73,10 @@ typedef struct {
                                  (construct_B), every proposal scored from scratch, sets limited to 12 parents / 48
                                  design columns.  <= 0 (the reference CLI's default -1): the reference builds an EMPTY
                                  design -- flat likelihood -- reproduced as is (quirk Q2) */
-    int32_t max_indegree;     /* scratch capacity for |S'| (0 = min(V, 64)); sets may still hold up to V parents
-                                 only if <= this bound */
+    int32_t max_indegree;     /* bound on |S| (0 = min(V, 128), the most the factor arena supports).  A proposal that would
+                                 grow a set beyond the bound is REJECTED (counted in n_indegree_rejects): the chain samples
+                                 the posterior truncated at |S| <= max_indegree, never an invalid run.  The reference has
+                                 no bound; with the default it is not reached unless V > 128 */
     double  large_indeg;      /* --large-indeg   (SSPS.jl:64-67)  */
     double  lambda_max;       /* --lambda-max    (SSPS.jl:68-70)  */
     double  lambda_prop_std;  /* --lambda-prop-std (SSPS.jl:75-78) */
@@ -81,8 +84,16 @@ typedef struct {
                                  (0 = default 250, <0 = never) */
     int32_t record_changepoints; /* 1: keep the reference's change-point log (small runs only) */
     int32_t collect_khist;    /* 1: histogram of proposed |S'| (diagnostics; slower) */
-    int32_t verify;           /* 1: additionally score EVERY proposal from scratch (O(k^3)) and count proposals whose
-                                 incrementally maintained factor gives a different score (diagnostics; much slower) */
+    int32_t verify;           /* 1: additionally (a) score EVERY proposal from scratch (O(k^3)) and count proposals whose
+                                 incrementally maintained factor gives a different score, (b) redo EVERY acceptance test
+                                 (parent-set and lambda moves) in the reference order with fp64 logarithms and count
+                                 decisions that differ from the screened test (diagnostics; much slower) */
+    double  min_burnin;       /* smallest burn-in fraction later passed to ssps_psrf* / ssps_edge_posterior (0 = 0.5,
+                                 the reference's default, postprocess_samples.jl:272): tally snapshots older than
+                                 min_burnin * samples are recycled first when the snapshot pool is full */
+    int32_t snapshot_slots;   /* size of the tally-snapshot pool, allocated ONCE by ssps_init_chains (0 = 32, clamped to
+                                 a quarter of the free device memory, at least 4); ssps_run never allocates */
+    int32_t reserved0;
 } ssps_config;
 
 typedef struct {
@@ -104,6 +115,20 @@ typedef struct {
     int64_t big_cycles;         /* warp cycles spent in the cooperative global-memory tier (clock64, summed over warps) */
     int64_t n_mismatch;         /* verify = 1 only: proposals whose cached-factor score differs from the from-scratch
                                    score of the same parent list by even one bit (must be 0) */
+    int64_t n_decision_mismatch;        /* verify = 1 only: parent-set moves whose screened accept/reject differs from the
+                                           reference-order fp64 test log(u) < alpha (must be 0) */
+    int64_t n_lambda_decision_mismatch; /* verify = 1 only: the same for lambda moves (must be 0) */
+    double  margin_use_max;     /* verify = 1 only: max over screened parent-set tests of |screening error| / margin;
+                                   a decision can only flip when this exceeds 1 */
+    double  lambda_margin_use_max;      /* the same for lambda moves */
+    int64_t n_indegree_rejects; /* proposals rejected because |S'| would exceed max_indegree (0 unless V > 128 or the
+                                   caller lowered max_indegree) */
+    int64_t n_mid_steps;        /* proposals of lanes in the lane-owned MID tier (SSPS_KS < |S| < SSPS_KM) */
+    int64_t snapshot_slots;     /* size of the tally-snapshot pool of this handle */
+    int64_t snapshots_live;     /* snapshots currently held */
+    int64_t snapshot_grid;      /* current spacing of the snapshots in recorded samples (doubles when the pool fills) */
+    int64_t device_allocs_in_run;   /* device allocations made inside ssps_run / ssps_replay since ssps_init_chains
+                                       (change-point logging and replay uploads only; 0 on the Philox path) */
 } ssps_run_stats;
 
 const char* ssps_last_error(void);

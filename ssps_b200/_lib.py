@@ -11,6 +11,7 @@ import os
 from . import _build
 
 OK = 0
+ABI_VERSION = 3
 ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NOMEM, ERR_INDEGREE, ERR_UNAVAILABLE = -1, -2, -3, -4, -5, -6
 
 _dp = C.POINTER(C.c_double)
@@ -27,6 +28,7 @@ class Config(C.Structure):
         ("max_indegree", C.c_int32), ("large_indeg", C.c_double), ("lambda_max", C.c_double),
         ("lambda_prop_std", C.c_double), ("psrf_grid", C.c_int32), ("record_changepoints", C.c_int32),
         ("collect_khist", C.c_int32), ("verify", C.c_int32),
+        ("min_burnin", C.c_double), ("snapshot_slots", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 
@@ -38,6 +40,11 @@ class RunStats(C.Structure):
         ("algorithmic_flops", C.c_double), ("algorithmic_bytes", C.c_double), ("kernel_ms", C.c_double),
         ("kernel_launches", C.c_int64), ("mh_launches", C.c_int64),
         ("n_tier1", C.c_int64), ("n_lambda_exact", C.c_int64), ("n_big_steps", C.c_int64), ("big_cycles", C.c_int64), ("n_mismatch", C.c_int64),
+        ("n_decision_mismatch", C.c_int64), ("n_lambda_decision_mismatch", C.c_int64),
+        ("margin_use_max", C.c_double), ("lambda_margin_use_max", C.c_double),
+        ("n_indegree_rejects", C.c_int64), ("n_mid_steps", C.c_int64),
+        ("snapshot_slots", C.c_int64), ("snapshots_live", C.c_int64), ("snapshot_grid", C.c_int64),
+        ("device_allocs_in_run", C.c_int64),
     ]
 
 
@@ -105,8 +112,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
         f = getattr(L, name)          # AttributeError if the symbol is missing: fail loudly
         f.restype = res
         f.argtypes = args
-    if L.ssps_abi_version() != 2:
-        raise ImportError("libssps_b200.so ABI version %d, binding expects 2" % L.ssps_abi_version())
+    if L.ssps_abi_version() != ABI_VERSION:
+        raise ImportError("libssps_b200.so ABI version %d, binding expects %d" % (L.ssps_abi_version(), ABI_VERSION))
     _lib = L
     return L
 

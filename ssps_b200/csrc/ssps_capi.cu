@@ -61,7 +61,12 @@ int fail(int code, const char* fmt, ...) {
 // (measured: bench steps of 83 ms instead of 39).  A released block goes back to the cache; the same shapes come again.
 // Ordering: a block is only ever released by the handle that used it, after that handle's stream work on it was enqueued;
 // re-use inside the same handle is stream-ordered, and ssps_destroy synchronises the stream before its blocks are released.
+// The cache is BOUNDED: ssps_destroy first returns whatever an earlier handle left behind to the driver, so the cache
+// never holds more than the last destroyed handle's footprint (plus the small transient buffers released since), and
+// never more than SSPS_CACHE_BYTES (default: a quarter of the device's memory).  A host that shares the GPU (the Julia
+// process of INTEGRATION.md) can empty it at any time with ssps_release_cached_memory.
 thread_local cudaStream_t g_stream = nullptr;     // stream of the handle the calling thread is working on (bind)
+thread_local long long g_device_allocs = 0;       // cudaMalloc calls made through BlockCache::take on this thread
 
 class BlockCache {
 public:
@@ -82,6 +87,7 @@ public:
                 }
             }
         }
+        ++g_device_allocs;
         cudaError_t e = cudaMalloc(out, bytes);
         if (e != cudaSuccess) {         // give the cache back to the driver and try once more
             cudaGetLastError();
@@ -94,7 +100,7 @@ public:
         int dev = 0; cudaGetDevice(&dev);
         {
             std::lock_guard<std::mutex> g(mu_);
-            if (cached_ + bytes <= cap_) {
+            if (cached_ + bytes <= cap(dev)) {
                 Block b; b.p = p; b.ev = nullptr;
                 if (cudaEventCreateWithFlags(&b.ev, cudaEventDisableTiming) == cudaSuccess) {
                     if (cudaEventRecord(b.ev, g_stream) != cudaSuccess) { cudaGetLastError(); cudaEventDestroy(b.ev); b.ev = nullptr; cudaStreamSynchronize(g_stream); }
@@ -124,7 +130,18 @@ private:
     std::mutex mu_;
     std::map<std::pair<int, size_t>, std::vector<Block>> free_;
     size_t cached_ = 0;
-    size_t cap_ = (size_t)96 << 30;     // bytes kept at most (a B200 has 180 GB)
+    size_t cap_ = 0;                    // bytes kept at most; 0 = not yet sized
+    size_t cap(int) {                   // (called with mu_ held)
+        if (cap_ == 0) {
+            if (const char* e = getenv("SSPS_CACHE_BYTES")) cap_ = (size_t)strtoull(e, nullptr, 10);
+            if (cap_ == 0) {
+                size_t free_b = 0, total_b = 0;
+                if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); total_b = (size_t)64 << 30; }
+                cap_ = total_b / 4;
+            }
+        }
+        return cap_;
+    }
 };
 
 template <class T>
@@ -153,10 +170,14 @@ struct DevBuf {
     size_t bytes() const { return n * sizeof(T); }
 };
 
+// A copy of the per-chain tallies at recorded sample n: a slot of the handle's snapshot slab (one allocation made by
+// ssps_init_chains; ssps_run never allocates)
 struct Snapshot {
     int64_t n = 0;                 // recorded samples per chain at the time of the copy
-    DevBuf<uint32_t> counts;       // [chain][child][parent]
-    DevBuf<double> lam_sum, lam_sq;
+    int slot = -1;
+    uint32_t* counts = nullptr;    // [chain][child][parent]
+    double* lam_sum = nullptr;     // [chain][vertex]
+    double* lam_sq = nullptr;
 };
 
 struct ParentEvent { int64_t n; int32_t child, parent, value; };
@@ -209,9 +230,12 @@ struct ssps_handle {
 
     // ---- snapshots for split-PSRF / burn-in (K4) ----
     int64_t snap_grid = 0;          // in recorded samples; 0 = disabled
-    size_t snap_budget_bytes = 0;
-    std::vector<Snapshot> spare;    // allocated ahead: no cudaMalloc between the launches of run_sweeps
+    DevBuf<unsigned char> snap_slab;    // snap_slots x snap_per bytes
+    size_t snap_per = 0;
+    int snap_slots = 0;
+    std::vector<int> snap_free;     // unused slots
     std::vector<Snapshot> snaps;    // ascending n, all multiples of snap_grid
+    long long allocs_in_run = 0;    // device allocations made inside run_sweeps since ssps_init_chains
     DevBuf<double> sums_scratch, psrf_scratch, psrf_partial;
     DevBuf<unsigned long long> max_bits;
 
@@ -343,6 +367,9 @@ int finish_data(ssps_handle* h, const double* prior_host) {
 
     // SSPS.jl:169  lambda_min = log(max(V / large_indeg - 1, exp(0.5)))
     h->lambda_min = log(fmax((double)V / h->cfg.large_indeg - 1.0, exp(0.5)));
+    if (!(h->cfg.lambda_max > h->lambda_min))      // Gen.uniform(lambda_min, lambda_max) would have an empty support (dbn_models.jl:66-70)
+        return fail(SSPS_ERR_INVALID, "lambda_max=%g does not exceed lambda_min=log(max(V/large_indeg - 1, e^0.5))=%g (V=%d, large_indeg=%g)",
+                    h->cfg.lambda_max, h->lambda_min, V, h->cfg.large_indeg);
     SspsDev& d = h->dev;
     d.n = n; d.V = V; d.dn = (double)n; d.shrink = (double)n / ((double)n + 1.0); d.log1pn = log(1.0 + (double)n);
     d.lambda_min = h->lambda_min; d.lambda_max = h->cfg.lambda_max; d.sigma = h->cfg.lambda_prop_std;
@@ -350,11 +377,20 @@ int finish_data(ssps_handle* h, const double* prior_host) {
     d.grp_off = h->grp_off.p; d.grp_omc = h->grp_omc.p; d.grp_mult = h->grp_mult.p;
     d.mvP = h->mvP.p; d.mvLogP = h->mvLogP.p; d.logint = h->logint.p;
     d.fgrp_off = h->fgrp_off.p; d.fgrp = h->fgrp.p; d.lam_margin = h->lam_margin.p;
+    if (h->cfg.regression_deg <= 0) {
+        // quirk Q2: construct_B loops over 1:min(deg, k) = nothing, the design is n x 0 for EVERY parent set
+        // (dbn_distributions.jl:179-194), so lml = -1/2 n log(y'y): no projection (R := 0 makes every w and q vanish) and
+        // no width penalty (log(1 + n) := 0).  The ordinary cached-factor kernel then runs the prior-only chain with no
+        // limit on |S| (round 1 sent this through the 12-parent interaction path, which the reference's own default
+        // flags overflowed at once).
+        CK(cudaMemsetAsync(h->R.p, 0, h->R.bytes(), s));
+        d.log1pn = 0.0;
+    }
     h->poly.Xminus = h->Xminus.p; h->poly.Y = h->Y.p; h->poly.deg = h->cfg.regression_deg;
     h->has_data = true;
     // any chains belong to the previous data set
     h->n_chains = 0;
-    h->snaps.clear(); h->spare.clear();
+    h->snaps.clear(); h->snap_free.clear();
     return SSPS_OK;
 }
 
@@ -389,7 +425,7 @@ int ssps_create(const ssps_config* cfg, ssps_handle** out) {
     ssps_handle* h = new (std::nothrow) ssps_handle();
     if (!h) return fail(SSPS_ERR_NOMEM, "out of host memory");
     h->cfg = *cfg;
-    h->is_poly = cfg->regression_deg != 1;
+    h->is_poly = cfg->regression_deg >= 2;
     h->device = dev;
     cudaError_t e = cudaSetDevice(dev);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, dev);
@@ -404,6 +440,7 @@ void ssps_destroy(ssps_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    BlockCache::get().trim(h->device);      // what earlier handles left behind goes back to the driver: the cache holds ONE footprint
     g_stream = h->stream;
     delete h;
     g_stream = nullptr;
@@ -569,7 +606,7 @@ int ssps_score(ssps_handle* h, int32_t n_sets, const int32_t* child, const int32
 // ================================================================================================
 namespace {
 
-int reserve_snapshots(ssps_handle* h, size_t count);
+int reserve_snapshots(ssps_handle* h);
 
 // K4 reductions over chains: enough (edge, chain-chunk) threads to fill the GPU; one chunk when V^2 alone does
 void chain_chunks(const ssps_handle* h, size_t vv, int& chunks, int& chunk_len) {
@@ -585,11 +622,13 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     const int V = h->V;
     const size_t vv = (size_t)V * V;
     h->n_chains = 0;
-    h->snaps.clear(); h->spare.clear();
+    h->snaps.clear(); h->snap_free.clear();
     h->nch_pad = ((n_chains + 31) / 32) * 32;
-    int kcap = h->cfg.max_indegree > 0 ? h->cfg.max_indegree : std::min(V, 64);
+    // bound on |S|: the reference has none; the default is everything the factor arena supports (a lane owns up to SSPS_KU
+    // columns of 32 rows), i.e. V itself up to V = 128.  Proposals beyond the bound are rejected (ssps.h: max_indegree).
+    int kcap = h->cfg.max_indegree > 0 ? h->cfg.max_indegree : std::min(V, 32 * SSPS_KU);
     h->kcap = std::min(kcap, V);
-    if (h->kcap > 128) return fail(SSPS_ERR_UNSUPPORTED, "max_indegree=%d: the per-thread factor arena supports at most 128", h->kcap);
+    if (h->kcap > 32 * SSPS_KU) return fail(SSPS_ERR_UNSUPPORTED, "max_indegree=%d: the per-thread factor arena supports at most %d", h->kcap, 32 * SSPS_KU);
     CK(h->k.alloc((size_t)V * h->nch_pad)); CK(h->lambda.alloc((size_t)V * h->nch_pad));
     CK(h->slots.alloc(vv * h->nch_pad));
     CK(h->counts.alloc(vv * n_chains));
@@ -669,15 +708,12 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     h->thinning = 0; h->sweeps_done = 0; h->samples_recorded = 0;
     h->kernel_ms = 0.0; h->mh_launches = 0;
     h->snap_grid = h->cfg.psrf_grid == 0 ? 250 : (h->cfg.psrf_grid < 0 ? 0 : h->cfg.psrf_grid);
-    size_t free_b = 0, total_b = 0;
-    CK(cudaMemGetInfo(&free_b, &total_b));
-    free_b += BlockCache::get().cached_bytes(h->device);
-    h->snap_budget_bytes = free_b / 4;
 
     h->cp_parent.clear(); h->cp_lambda.clear(); h->cp_present.clear(); h->cp_lambda_last.clear();
     h->pev_cap = h->lev_cap = 0;
     h->n_chains = n_chains;
-    CKS(reserve_snapshots(h, 32));
+    CKS(reserve_snapshots(h));
+    h->allocs_in_run = 0;
     return SSPS_OK;
 }
 
@@ -786,52 +822,70 @@ int changepoints_drain(ssps_handle* h, int64_t rec_base) {
     return SSPS_OK;
 }
 
-// `count` more snapshot buffers ahead of need (bounded by the budget): cudaMalloc of these 100 MB-class blocks takes
-// 2..100 ms at random, which must not fall between the launches of run_sweeps
-int reserve_snapshots(ssps_handle* h, size_t count) {
+// The snapshot pool: ONE slab sized at ssps_init_chains, sub-allocated in fixed slots.  (Round 1 kept a copy of the
+// tallies every snap_grid samples forever and refilled its pool with cudaMalloc -- 2..180 ms at random between the
+// launches of ssps_run, 22-39 % of a driver-timed bench step.)
+int reserve_snapshots(ssps_handle* h) {
+    h->snaps.clear(); h->snap_free.clear();
+    h->snap_slots = 0; h->snap_per = 0;
     if (h->snap_grid <= 0 || h->n_chains <= 0) return SSPS_OK;
     const size_t vv = (size_t)h->V * h->V, nc = (size_t)h->n_chains;
-    const size_t per = vv * nc * sizeof(uint32_t) + 2 * (size_t)h->V * nc * sizeof(double);
-    const size_t have = h->snaps.size() + h->spare.size();
-    const size_t room = h->snap_budget_bytes / std::max<size_t>(per, 1);
-    count = std::min(count, room > have ? room - have : 0);
-    for (size_t e = 0; e < count; ++e) {
-        Snapshot sn;
-        CK(sn.counts.alloc(vv * nc)); CK(sn.lam_sum.alloc((size_t)h->V * nc)); CK(sn.lam_sq.alloc((size_t)h->V * nc));
-        h->spare.push_back(std::move(sn));
-    }
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+    const size_t per = up(vv * nc * sizeof(uint32_t)) + 2 * up((size_t)h->V * nc * sizeof(double));
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    free_b += BlockCache::get().cached_bytes(h->device);
+    int want = h->cfg.snapshot_slots > 0 ? h->cfg.snapshot_slots : 32;
+    if (const char* e = getenv("SSPS_SNAP_SLOTS")) want = atoi(e);      // experiments
+    const size_t room = (free_b / 4) / per;
+    int slots = (int)std::min<size_t>((size_t)std::max(want, 4), std::max<size_t>(room, 4));
+    CK(h->snap_slab.alloc((size_t)slots * per));
+    h->snap_per = per; h->snap_slots = slots;
+    for (int e = slots; e-- > 0;) h->snap_free.push_back(e);
     return SSPS_OK;
 }
 
+// Which snapshots can still be read?  A PSRF / posterior query at length L with burn-in fraction beta reads the
+// tallies at b = floor(beta L) and at the split point b + (L - b) / 2 (evaluate_convergence,
+// postprocess_samples.jl:155-180); L is the current length or, when that is not snapshot-aligned, the last aligned
+// one (at most 4 grid steps back).  So with beta >= min_burnin a snapshot older than min_burnin (n - 4 g) is dead.
+// When the pool is full: recycle the dead ones; if none, drop every other snapshot and double the grid.
 int take_snapshot(ssps_handle* h) {
-    const size_t vv = (size_t)h->V * h->V;
-    const size_t per = vv * h->n_chains * sizeof(uint32_t) + 2 * (size_t)h->V * h->n_chains * sizeof(double);
-    // keep within budget: drop every other snapshot and double the grid
-    while (h->snap_grid > 0 && (h->snaps.size() + 1) * per > h->snap_budget_bytes && h->snaps.size() >= 2) {
-        h->snap_grid *= 2;
+    if (h->snap_grid == 0 || h->snap_slots == 0 || h->samples_recorded % h->snap_grid != 0) return SSPS_OK;
+    const double beta = h->cfg.min_burnin > 0.0 ? std::min(h->cfg.min_burnin, 0.95) : 0.5;
+    while (h->snap_free.empty()) {
+        const int64_t dead_below = (int64_t)floor(beta * (double)std::max<int64_t>(h->samples_recorded - 4 * h->snap_grid, 0));
         std::vector<Snapshot> kept;
         for (auto& s : h->snaps) {
-            if (s.n % h->snap_grid == 0) kept.push_back(std::move(s));
-            else h->spare.push_back(std::move(s));      // same stream: safe to overwrite in order
+            if (s.n < dead_below) h->snap_free.push_back(s.slot);      // same stream: safe to overwrite in order
+            else kept.push_back(s);
+        }
+        if (h->snap_free.empty()) {
+            h->snap_grid *= 2;
+            kept.clear();
+            for (auto& s : h->snaps) {
+                if (s.n % h->snap_grid == 0) kept.push_back(s);
+                else h->snap_free.push_back(s.slot);
+            }
+            if (getenv("SSPS_TRACE"))
+                fprintf(stderr, "[ssps trace] snapshot pool full at n = %lld: grid doubled to %lld\n", (long long)h->samples_recorded, (long long)h->snap_grid);
         }
         h->snaps.swap(kept);
+        if (h->samples_recorded % h->snap_grid != 0) return SSPS_OK;       // no longer a grid point
     }
-    if (h->snap_grid == 0 || h->samples_recorded % h->snap_grid != 0) return SSPS_OK;
-    if (h->spare.empty()) {
-        const auto ta = std::chrono::steady_clock::now();
-        CKS(reserve_snapshots(h, 16));
-        if (getenv("SSPS_TRACE"))
-            fprintf(stderr, "[ssps trace] snapshot refill %.1f ms (n = %lld)\n",
-                    1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - ta).count(), (long long)h->samples_recorded);
-    }
+    const size_t vv = (size_t)h->V * h->V, nc = (size_t)h->n_chains;
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
     Snapshot sn;
-    if (!h->spare.empty()) { sn = std::move(h->spare.back()); h->spare.pop_back(); }
-    else { CK(sn.counts.alloc(vv * h->n_chains)); CK(sn.lam_sum.alloc((size_t)h->V * h->n_chains)); CK(sn.lam_sq.alloc((size_t)h->V * h->n_chains)); }
+    sn.slot = h->snap_free.back(); h->snap_free.pop_back();
+    unsigned char* base = h->snap_slab.p + (size_t)sn.slot * h->snap_per;
+    sn.counts = (uint32_t*)base;
+    sn.lam_sum = (double*)(base + up(vv * nc * sizeof(uint32_t)));
+    sn.lam_sq = (double*)(base + up(vv * nc * sizeof(uint32_t)) + up((size_t)h->V * nc * sizeof(double)));
     sn.n = h->samples_recorded;
-    CK(cudaMemcpyAsync(sn.counts.p, h->counts.p, vv * h->n_chains * sizeof(uint32_t), cudaMemcpyDeviceToDevice, h->stream));
-    CK(cudaMemcpyAsync(sn.lam_sum.p, h->lam_sum.p, (size_t)h->V * h->n_chains * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
-    CK(cudaMemcpyAsync(sn.lam_sq.p, h->lam_sq.p, (size_t)h->V * h->n_chains * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
-    h->snaps.push_back(std::move(sn));
+    CK(cudaMemcpyAsync(sn.counts, h->counts.p, vv * nc * sizeof(uint32_t), cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpyAsync(sn.lam_sum, h->lam_sum.p, (size_t)h->V * nc * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpyAsync(sn.lam_sq, h->lam_sq.p, (size_t)h->V * nc * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    h->snaps.push_back(sn);
     return SSPS_OK;
 }
 
@@ -859,6 +913,7 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
     if (replay_host) CKS(upload(h, replay_dev, replay_host, (size_t)n_sweeps * C * V * 6));
 
     const auto t0 = std::chrono::steady_clock::now();
+    const long long allocs0 = g_device_allocs;
     int64_t done = 0;
     size_t ev_used = 0;
     while (done < n_sweeps) {
@@ -946,9 +1001,8 @@ int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning,
     }
     for (size_t e = 0; e < ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
     if (sweeps_done_out) *sweeps_done_out = done;
-    unsigned long long overflow = 0;
-    CK(cudaMemcpy(&overflow, h->stats.p + ST_OVERFLOW, sizeof overflow, cudaMemcpyDeviceToHost));
-    if (overflow) return fail(SSPS_ERR_INDEGREE, "a parent set exceeded max_indegree=%d; results are invalid, re-create with a larger bound", h->kcap);
+    h->allocs_in_run += g_device_allocs - allocs0;
+    // (a proposal that would exceed max_indegree is rejected and counted -- ST_KCAP_REJECT -- never an error after the fact)
     return SSPS_OK;
 }
 
@@ -990,11 +1044,31 @@ int ssps_init_chains(ssps_handle* h, int32_t n_chains, uint64_t seed, uint32_t c
         CKS(upload(h, d_lam, init_lambda, nmc));
         import_state_kernel<<<blocks, 128, 0, h->stream>>>(h->dev, h->st, d_off.p, d_mem.p, d_lam.p);
         CKS(launch_ok(h, "import_state"));
-        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaStreamSynchronize(h->stream));       // the uploads go out of scope
     } else {
         init_chains_kernel<<<blocks, 128, 0, h->stream>>>(h->dev, h->st, seed, chain_id_offset);
         CKS(launch_ok(h, "init_chains"));
+    }
+    // the initial sets must fit the bound the sweeps run under: refuse HERE, not after hours of sampling
+    {
+        int kmax = 0;
+        CK(cudaMemsetAsync(h->task_counter.p, 0, sizeof(int), h->stream));
+        max_indegree_kernel<<<blocks, 128, 0, h->stream>>>(h->st, V, h->task_counter.p);
+        CKS(launch_ok(h, "max_indegree"));
+        CK(cudaMemcpyAsync(&kmax, h->task_counter.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
         CK(cudaStreamSynchronize(h->stream));
+        int bound = h->kcap;
+        const char* why = "max_indegree";
+        if (h->is_poly) {
+            // interaction columns: the widest design a set of kmax parents needs must fit the from-scratch scorer
+            if (kmax > SSPS_POLY_KMAX || poly_width(kmax, h->cfg.regression_deg) < 0) { bound = std::min(bound, SSPS_POLY_KMAX); why = "the interaction-column scorer's limit"; }
+        }
+        if (kmax > bound || (h->is_poly && poly_width(kmax, h->cfg.regression_deg) < 0)) {
+            h->n_chains = 0;
+            return fail(SSPS_ERR_INDEGREE, "an initial parent set has %d members, above %s (%d%s); lower the prior's in-degree "
+                        "(--large-indeg) or raise max_indegree", kmax, why, bound,
+                        h->is_poly ? ", or fewer if the design would exceed the column limit" : "");
+        }
     }
     return SSPS_OK;
 }
@@ -1124,7 +1198,7 @@ int ssps_edge_posterior(ssps_handle* h, double burnin, double* probs_child_major
         int chunks = 1, chunk_len = h->n_chains;
         chain_chunks(h, vv, chunks, chunk_len);
         CK(cudaMemsetAsync(out.p, 0, out.bytes(), h->stream));
-        edge_sum_kernel<<<dim3(div_up(vv, 256), chunks), 256, 0, h->stream>>>(h->counts.p, lo ? lo->counts.p : nullptr, h->n_chains, vv, chunk_len, out.p);
+        edge_sum_kernel<<<dim3(div_up(vv, 256), chunks), 256, 0, h->stream>>>(h->counts.p, lo ? lo->counts : nullptr, h->n_chains, vv, chunk_len, out.p);
         CKS(launch_ok(h, "edge_sum"));
         CKS(download(h, probs_child_major, out.p, vv));
         CK(cudaStreamSynchronize(h->stream));
@@ -1133,7 +1207,7 @@ int ssps_edge_posterior(ssps_handle* h, double burnin, double* probs_child_major
     if (lambda_mean) {
         DevBuf<double> out;
         CK(out.alloc(h->V));
-        lam_sum_kernel<<<h->V, 256, 0, h->stream>>>(h->lam_sum.p, lo ? lo->lam_sum.p : nullptr, h->n_chains, h->V, out.p);
+        lam_sum_kernel<<<h->V, 256, 0, h->stream>>>(h->lam_sum.p, lo ? lo->lam_sum : nullptr, h->n_chains, h->V, out.p);
         CKS(launch_ok(h, "lam_sum"));
         CKS(download(h, lambda_mean, out.p, (size_t)h->V));
         CK(cudaStreamSynchronize(h->stream));
@@ -1177,15 +1251,15 @@ int ssps_psrf_sums(ssps_handle* h, double burnin, double* sums, int32_t on_devic
     double* dst = sums;
     if (!on_device) { CK(h->sums_scratch.alloc(total)); dst = h->sums_scratch.p; }
     const double N1 = (double)(s - b), N2 = (double)(len - s);
-    const uint32_t* c_len = S_len ? S_len->counts.p : h->counts.p;
-    const double* ls_len = S_len ? S_len->lam_sum.p : h->lam_sum.p;
-    const double* lq_len = S_len ? S_len->lam_sq.p : h->lam_sq.p;
+    const uint32_t* c_len = S_len ? S_len->counts : h->counts.p;
+    const double* ls_len = S_len ? S_len->lam_sum : h->lam_sum.p;
+    const double* lq_len = S_len ? S_len->lam_sq : h->lam_sq.p;
     {
         int chunks = 1, chunk_len = h->n_chains;
         chain_chunks(h, vv, chunks, chunk_len);
         double* part = dst;
         if (chunks > 1) { CK(h->psrf_partial.alloc((size_t)chunks * 3 * vv)); part = h->psrf_partial.p; }
-        psrf_sums_kernel<<<dim3(div_up(vv, 256), chunks), 256, 0, h->stream>>>(c_len, S_s->counts.p, S_b ? S_b->counts.p : nullptr, h->n_chains, vv,
+        psrf_sums_kernel<<<dim3(div_up(vv, 256), chunks), 256, 0, h->stream>>>(c_len, S_s->counts, S_b ? S_b->counts : nullptr, h->n_chains, vv,
                                                                                 N1, N2, chunk_len, part);
         CKS(launch_ok(h, "psrf_sums"));
         if (chunks > 1) {
@@ -1193,8 +1267,8 @@ int ssps_psrf_sums(ssps_handle* h, double burnin, double* sums, int32_t on_devic
             CKS(launch_ok(h, "psrf_sums_reduce"));
         }
     }
-    psrf_lambda_sums_kernel<<<V, 256, 0, h->stream>>>(ls_len, S_s->lam_sum.p, S_b ? S_b->lam_sum.p : nullptr, lq_len,
-                                                                        S_s->lam_sq.p, S_b ? S_b->lam_sq.p : nullptr, h->n_chains, V, N1, N2,
+    psrf_lambda_sums_kernel<<<V, 256, 0, h->stream>>>(ls_len, S_s->lam_sum, S_b ? S_b->lam_sum : nullptr, lq_len,
+                                                                        S_s->lam_sq, S_b ? S_b->lam_sq : nullptr, h->n_chains, V, N1, N2,
                                                                         dst + 3 * vv);
     CKS(launch_ok(h, "psrf_lambda_sums"));
     // tail: number of half-chains H, and H * n (so that a SUM all-reduce over ranks keeps n = tail[1] / tail[0])
@@ -1304,8 +1378,8 @@ int ssps_get_stats(ssps_handle* h, ssps_run_stats* out) {
     out->kernel_launches = h->kernel_launches;
     if (h->n_chains > 0) {
         unsigned long long st[ST_N];
+        CK(cudaMemcpyAsync(st, h->stats.p, sizeof st, cudaMemcpyDeviceToHost, h->stream));     // (on the handle's stream: no device-wide sync)
         CK(cudaStreamSynchronize(h->stream));
-        CK(cudaMemcpy(st, h->stats.p, sizeof st, cudaMemcpyDeviceToHost));
         out->sweeps_done = h->sweeps_done;
         out->samples_recorded = h->samples_recorded;
         out->n_proposals = (int64_t)st[ST_PROP];
@@ -1319,6 +1393,16 @@ int ssps_get_stats(ssps_handle* h, ssps_run_stats* out) {
         out->big_cycles = (int64_t)st[ST_BIG_CYCLES];
         out->kernel_ms = h->kernel_ms;
         out->mh_launches = h->mh_launches;
+        out->n_decision_mismatch = (int64_t)st[ST_DEC_MISMATCH];
+        out->n_lambda_decision_mismatch = (int64_t)st[ST_LAM_DEC_MISMATCH];
+        { uint32_t b = (uint32_t)st[ST_MARGIN_USE]; float f; memcpy(&f, &b, sizeof f); out->margin_use_max = (double)f; }
+        { uint32_t b = (uint32_t)st[ST_LAM_MARGIN_USE]; float f; memcpy(&f, &b, sizeof f); out->lambda_margin_use_max = (double)f; }
+        out->n_indegree_rejects = (int64_t)st[ST_KCAP_REJECT];
+        out->n_mid_steps = (int64_t)st[ST_MID_STEPS];
+        out->snapshot_slots = h->snap_slots;
+        out->snapshots_live = (int64_t)h->snaps.size();
+        out->snapshot_grid = h->snap_grid;
+        out->device_allocs_in_run = h->allocs_in_run;
     }
     return SSPS_OK;
 }
@@ -1327,8 +1411,8 @@ int ssps_get_raw_stats(ssps_handle* h, int64_t* out, int32_t len) {
     CKS(bind(h));
     if (!out || len < 1 || h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "bad buffer or no chains");
     unsigned long long st[ST_N];
+    CK(cudaMemcpyAsync(st, h->stats.p, sizeof st, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy(st, h->stats.p, sizeof st, cudaMemcpyDeviceToHost));
     for (int a = 0; a < len; ++a) out[a] = a < ST_N ? (int64_t)st[a] : 0;
     return SSPS_OK;
 }
@@ -1338,8 +1422,8 @@ int ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len) {
     if (!hist || len < 1) return fail(SSPS_ERR_INVALID, "bad buffer");
     if (h->n_chains <= 0 || !h->cfg.collect_khist) return fail(SSPS_ERR_UNAVAILABLE, "collect_khist was 0 or no chains");
     unsigned long long hh[64];
+    CK(cudaMemcpyAsync(hh, h->khist.p, sizeof hh, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy(hh, h->khist.p, sizeof hh, cudaMemcpyDeviceToHost));
     for (int a = 0; a < len; ++a) hist[a] = a < 64 ? (int64_t)hh[a] : 0;
     return SSPS_OK;
 }

@@ -323,6 +323,16 @@ __global__ void init_chains_kernel(SspsDev P, ChainState st, uint64_t seed, uint
     st.lambda[(size_t)vertex * st.nch_pad + chain] = lam;
 }
 
+// largest in-degree over all micro-chains (ssps_init_chains checks it against max_indegree before any sweep runs)
+__global__ void max_indegree_kernel(ChainState st, int V, int* __restrict__ out) {
+    const size_t m = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int chain = (int)(m % st.nch_pad), vertex = (int)(m / st.nch_pad);
+    int k = 0;
+    if (vertex < V && chain < st.n_chains) k = st.k[(size_t)vertex * st.nch_pad + chain];
+    k = __reduce_max_sync(0xffffffffu, k);
+    if ((threadIdx.x & 31) == 0 && k > 0) atomicMax(out, k);
+}
+
 // ------------------------------------------------------------------------------------------------
 // state read-back helpers
 // ------------------------------------------------------------------------------------------------

@@ -58,8 +58,11 @@
 
 enum { MODE_SMALL = 0, MODE_BIG = 1, MODE_PROMOTE = 2 };
 // stats slots (unsigned long long each)
-enum { ST_ACCP = 0, ST_ACCL = 1, ST_SUMK = 2, ST_F3 = 3, ST_BYTES = 4, ST_OVERFLOW = 5, ST_PROP = 6, ST_TIER1 = 7,
-       ST_MISMATCH = 10, ST_BIG_CYCLES = 11, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_MID_STEPS = 14, ST_MID_CYCLES = 15, ST_PROF = 16, ST_N = 32 };
+enum { ST_ACCP = 0, ST_ACCL = 1, ST_SUMK = 2, ST_F3 = 3, ST_BYTES = 4, ST_KCAP_REJECT = 5, ST_PROP = 6, ST_TIER1 = 7,
+       ST_MISMATCH = 10, ST_BIG_CYCLES = 11, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_MID_STEPS = 14, ST_MID_CYCLES = 15, ST_PROF = 16,
+       ST_DEC_MISMATCH = 24, ST_LAM_DEC_MISMATCH = 25,      // VERIFY: screened decision != reference-order fp64 decision
+       ST_MARGIN_USE = 26, ST_LAM_MARGIN_USE = 27,          // VERIFY: max |screening error| / margin as float bits (low word)
+       ST_N = 32 };
 
 __device__ __forceinline__ float fast_lg2(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float fast_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -309,13 +312,15 @@ __device__ __noinline__ double sorted_somc(const SspsDev& P, const int child, co
 // lambda move in the reference order (the oracle's chain_step restates exactly this); xs.S(0..k-1)
 // holds the SORTED current set
 __device__ __noinline__ int lambda_exact_decide(const SspsDev& P, const int child, const Scratch& xs, const int k, const double lam,
-                                                const double lam_new, const double u_lam) {
+                                                const double lam_new, const double u_lam, double* diff_out) {
     const double* __restrict__ omc_i = P.omc + (size_t)P.V * child;
     double somc = 0.0;
     for (int a = 0; a < k; ++a) somc += __ldg(omc_i + xs.S(a));
     const double nrm = prior_normaliser(P, child, lam), nrm_new = prior_normaliser(P, child, lam_new);
     const double w = -(lam_new - lam) * somc - (nrm_new - nrm);
-    return log(u_lam) < w ? 1 : 0;
+    const double lu = log(u_lam);
+    if (diff_out) *diff_out = lu - w;
+    return lu < w ? 1 : 0;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -371,6 +376,7 @@ __device__ __noinline__ int mh_accept_exact(const double log1pn, const double dn
     return log(u_acc) < alpha ? 1 : 0;
 }
 
+template <bool VERIFY>
 __device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
                                           const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
                                           const double ip_new, const float lg_new, const double u_acc, unsigned long long* stats) {
@@ -391,15 +397,28 @@ __device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, co
         const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
         accept = log(u_acc) < alpha;
 #endif
+        if (VERIFY) return accept;          // already the reference-order test
+    }
+    if (VERIFY) {       // the DECISION re-derived in the reference order (Gen.mh: log(rand()) < alpha) for every screened test
+        const double lml_cur = -0.5 * (double)k * P.log1pn - 0.5 * P.dn * log(ip_cur);
+        const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
+        const double w = dprior + (lml_new - lml_cur);
+        const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
+        const double lu = log(u_acc);
+        if ((lu < alpha) != accept) atomicAdd(stats + ST_DEC_MISMATCH, 1ull);
+        // how much of its margin the screening used: a flip needs |error| > |diff| > margin, i.e. a ratio above 1
+        const float use = (float)(fabs(diff - (lu - alpha)) / marg);
+        atomicMax((unsigned*)(stats + ST_MARGIN_USE), __float_as_uint(use));
     }
     return accept;
 }
 
 // out-of-line copy for the rare tiers (mid_move, big_phase): 320 instructions per inlined instance
+template <bool VERIFY>
 __device__ __noinline__ bool mh_accept_ool(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
                                            const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
                                            const double ip_new, const float lg_new, const double u_acc, unsigned long long* stats) {
-    return mh_accept(P, action, k, kn, dprior, fwd, bwd, ip_cur, lg_ip_cur, ip_new, lg_new, u_acc, stats);
+    return mh_accept<VERIFY>(P, action, k, kn, dprior, fwd, bwd, ip_cur, lg_ip_cur, ip_new, lg_new, u_acc, stats);
 }
 
 __device__ __forceinline__ void lane_set_q(const SspsDev& P, int child, Lane& L, double q) {
@@ -514,7 +533,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     double nl[SSPS_TRI(KS) - KS + 1], ninv[KS], nw[KS];
     const int kr_max = __reduce_max_sync(peers, kr);
     const int p_min = __reduce_min_sync(peers, p);
-    if (kn > C.kcap) { atomicExch(C.stats + ST_OVERFLOW, 1ull); return 0; }      // (after the warp collectives)
+    if (kn > C.kcap) { atomicAdd(C.stats + ST_KCAP_REJECT, 1ull); return 0; }      // (after the warp collectives)
 #pragma unroll
     for (int a = 0; a < KS; ++a) {
         ninv[a] = 0.0; nw[a] = 0.0;
@@ -597,7 +616,7 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
     }
     const double ip_new = C.yty - P.shrink * q_new;
     const float lg_new = fast_lg2((float)ip_new);
-    const bool accept = mh_accept(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats);
+    const bool accept = mh_accept<VERIFY>(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats);
 
     if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
         int t = 0;
@@ -719,7 +738,7 @@ __device__ __noinline__ int mid_move(const SspsDev& P, const int child, const St
     const int kr = k - (has_rem ? 1 : 0);
     const int kn = kr + (has_add ? 1 : 0);
     kn_out = kn;
-    if (kn > C.kcap) { atomicExch(C.stats + ST_OVERFLOW, 1ull); return 0; }
+    if (kn > C.kcap) { atomicAdd(C.stats + ST_KCAP_REJECT, 1ull); return 0; }
     const double fwd = mv.fwd, bwd = mv.bwd;
     const double* __restrict__ omc_i = P.omc + (size_t)V * child;
     const double* __restrict__ Ri = P.R + (size_t)V * child;
@@ -764,7 +783,7 @@ SSPS_UNROLL_MID
     }
     const double ip_new = C.yty - P.shrink * q_new;
     const float lg_new = fast_lg2((float)ip_new);
-    const bool accept = mh_accept_ool(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats);
+    const bool accept = mh_accept_ool<VERIFY>(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats);
 
     if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
         int t = 0;
@@ -1058,7 +1077,7 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
         const int kn = k + (has_add ? 1 : 0) - (has_rem ? 1 : 0);
         ++n_big;
         if (kn > C.kcap) {
-            if (lane == src) { atomicExch(C.stats + ST_OVERFLOW, 1ull); *acc_kn = kn << 1; }
+            if (lane == src) { atomicAdd(C.stats + ST_KCAP_REJECT, 1ull); *acc_kn = kn << 1; }
             continue;
         }
 
@@ -1128,7 +1147,7 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
             if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
             const double ip_new = C.yty - P.shrink * q_new;
             const float lg_new = fast_lg2((float)ip_new);
-            acc = mh_accept_ool(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats) ? 1 : 0;
+            acc = mh_accept_ool<VERIFY>(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats) ? 1 : 0;
             if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
                 const Scratch xs = C.xs_of(lane);
                 for (int b = 0; b < kn; ++b) xs.T(b) = (uint16_t)T.idof(b);
@@ -1293,7 +1312,7 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
         L.ip = 0.0; L.lg_ip = 0.f; L.somc = 0.0; L.nrmf = 0.0; L.mode = MODE_SMALL;
         if (live) {
             L.k = st.k[sidx]; L.lam = st.lambda[sidx];
-            if (L.k > prm.kcap) { atomicExch(prm.stats + ST_OVERFLOW, 1ull); live = false; L.k = 0; }
+            if (L.k > prm.kcap) live = false;       // cannot happen: ssps_init_chains refuses initial sets above max_indegree
         }
         if (live) {     // parent list: id | rank << 16, arrival order
             if (L.k <= SSPS_KS) {
@@ -1337,11 +1356,19 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
                     const float lgu = fast_lg2((float)d.u_lam);
                     const double diff = SSPS_LN2 * (double)lgu - w;
                     bool acc = diff < 0.0;
-                    if (!(d.u_lam > 1e-30 && fabs(diff) > (double)lmarg + 1.2e-6 * ((double)fabsf(lgu) + 1.0) + 1e-9 * fabs(w))) {
+                    const double lmg = (double)lmarg + 1.2e-6 * ((double)fabsf(lgu) + 1.0) + 1e-9 * fabs(w);
+                    if (!(d.u_lam > 1e-30 && fabs(diff) > lmg)) {
                         const Scratch xs = C.xs_of(lane);
                         write_sorted(L.mode, S, C.big(lane), xs, L.k);
-                        acc = lambda_exact_decide(P, i, xs, L.k, L.lam, lam_new, d.u_lam) != 0;
+                        acc = lambda_exact_decide(P, i, xs, L.k, L.lam, lam_new, d.u_lam, nullptr) != 0;
                         atomicAdd(prm.stats + ST_LAM_EXACT, 1ull);
+                    } else if (VERIFY) {    // the screened decision against the reference-order fp64 test
+                        const Scratch xs = C.xs_of(lane);
+                        write_sorted(L.mode, S, C.big(lane), xs, L.k);
+                        double dx = 0.0;
+                        const bool ex = lambda_exact_decide(P, i, xs, L.k, L.lam, lam_new, d.u_lam, &dx) != 0;
+                        if (ex != acc) atomicAdd(prm.stats + ST_LAM_DEC_MISMATCH, 1ull);
+                        atomicMax((unsigned*)(prm.stats + ST_LAM_MARGIN_USE), __float_as_uint((float)(fabs(diff - dx) / lmg)));
                     }
                     if (acc) { L.lam = lam_new; L.nrmf = nrm_new; ++s_accl; }
                 }

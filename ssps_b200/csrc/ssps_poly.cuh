@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(128) mh_poly_kernel(const __grid_constant__ Ss
         uint32_t* pev = prm.pev ? prm.pev + mc * prm.pev_cap : nullptr;
         int k = st.k[sidx];
         double lam = st.lambda[sidx];
-        if (k > SSPS_POLY_KMAX || (Q.deg > 0 && poly_width(k, Q.deg) < 0)) { atomicExch(prm.stats + ST_OVERFLOW, 1ull); continue; }
+        if (k > SSPS_POLY_KMAX || (Q.deg > 0 && poly_width(k, Q.deg) < 0)) continue;    // cannot happen: refused by ssps_init_chains
         int S[SSPS_POLY_KMAX], T[SSPS_POLY_KMAX];
         for (int a = 0; a < k; ++a) S[(int)(slot_ref(st, V, i, a, chain) >> 16)] = (int)(slot_ref(st, V, i, a, chain) & 0xffffu);
         const double* __restrict__ omc_i = P.omc + (size_t)V * i;
@@ -241,17 +241,19 @@ __global__ void __launch_bounds__(128) mh_poly_kernel(const __grid_constant__ Ss
                 const unsigned long long m_ = (unsigned long long)mw;
                 s_f3 += 3ull * (unsigned long long)P.n * m_ * (m_ + 5ull) + m_ * m_ * m_ + 6ull * m_ * m_ + 6ull * m_;
             }
-            if (kn > SSPS_POLY_KMAX || kn > prm.kcap || mw < 0) { atomicExch(prm.stats + ST_OVERFLOW, 1ull); continue; }
+            // a proposal beyond the path's bounds is rejected and counted (ssps.h: max_indegree), the sweep goes on
+            const bool in_range = !(kn > SSPS_POLY_KMAX || kn > prm.kcap || mw < 0);
+            if (!in_range) atomicAdd(prm.stats + ST_KCAP_REJECT, 1ull);
             double fwd, bwd;
             move_ratio(P, i, k, action, fwd, bwd);
             double dprior = 0.0;
             if (has_add) dprior = -lam * __ldg(omc_i + j_add);
             if (has_rem) dprior = dprior + lam * __ldg(omc_i + j_rem);
-            const double lml_new = poly_score_set(P, Q, i, T, kn, sc);
+            const double lml_new = in_range ? poly_score_set(P, Q, i, T, kn, sc) : lml;
             const double w = dprior + (lml_new - lml);
             const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
             const int rel_now = ceil_div_i(l, thin) - 1;
-            if (log(d.u_acc) < alpha) {
+            if (in_range && log(d.u_acc) < alpha) {
                 ++s_accp;
                 if (pev) {
                     if (has_rem && n_pev < prm.pev_cap) pev[n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);

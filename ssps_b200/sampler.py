@@ -68,7 +68,7 @@ class Sampler:
     def __init__(self, device: int = -1, regression_deg: int = 1, large_indeg: float = 20.0,
                  lambda_max: float = 15.0, lambda_prop_std: float = 0.25, max_indegree: int = 0,
                  psrf_grid: int = 0, record_changepoints: bool = False, collect_khist: bool = False,
-                 verify: bool = False):
+                 verify: bool = False, min_burnin: float = 0.0, snapshot_slots: int = 0):
         self._L = _lib.load()
         cfg = Config()
         cfg.struct_size = C.sizeof(Config)
@@ -82,6 +82,8 @@ class Sampler:
         cfg.record_changepoints = int(record_changepoints)
         cfg.collect_khist = int(collect_khist)
         cfg.verify = int(verify)
+        cfg.min_burnin = float(min_burnin)
+        cfg.snapshot_slots = int(snapshot_slots)
         self._h = C.c_void_p()
         check(self._L.ssps_create(C.byref(cfg), C.byref(self._h)))
         self.cfg = cfg

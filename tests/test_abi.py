@@ -25,14 +25,14 @@ def test_header_symbols_are_exported_and_bound():
         assert hasattr(raw, n), "library does not export %s" % n
         assert n in _lib.SIGNATURES, "binding misses %s" % n
     assert set(_lib.SIGNATURES) == set(names)
-    assert L.ssps_abi_version() == 2
+    assert L.ssps_abi_version() == 3
     assert L.ssps_psrf_sums_len(10) == 3 * 100 + 30 + 2
 
 
 def test_struct_layouts_match_header():
     from ssps_b200 import _lib
-    assert ctypes.sizeof(_lib.Config) == 56
-    assert ctypes.sizeof(_lib.RunStats) == 88 + 5 * 8
+    assert ctypes.sizeof(_lib.Config) == 72
+    assert ctypes.sizeof(_lib.RunStats) == 88 + 5 * 8 + 10 * 8
 
 
 def test_no_cpu_fallback_without_gpu():

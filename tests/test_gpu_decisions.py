@@ -1,0 +1,181 @@
+"""Level-2 parity at the rates the kernel runs at, and on the configurations the bench measures.
+
+(i)   verify=1 launches re-derive, for EVERY proposal, the score from scratch (bitwise) AND the accept/reject decision in
+      the reference order with fp64 logarithms (Gen.mh: log(rand()) < alpha; call sites SSPS/src/state_updates.jl:44-47).
+      The fp32-screened test of mh_accept / the lambda move may only differ from it if the screening error exceeds its
+      margin; `margin_use_max` reports how much of the margin the worst screened test used.
+(ii)  bit-exact replay against the oracle at the metric point (V=100, n=28), C4 (V=200, n=396) and V=1000 (deg 1).
+(iii) the genie artefact of the reference's own run (tests/baseline_predictions.genie -> tests/golden/example_c1.npz),
+      the only reference-PRODUCED numbers that exist: loose L3 check of the converged GPU posterior on C1.
+"""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from conftest import make_synth  # noqa: E402
+
+
+def _draws(rng, n_sweeps, n_chains, V):
+    d = rng.random((n_sweeps, n_chains, V, 6))
+    d[..., 0] = rng.standard_normal((n_sweeps, n_chains, V))
+    return d
+
+
+def _verified_run(s, n_chains, n_sweeps, seed, batch=2000):
+    s.generate(n_chains, seed=seed)
+    done = 0
+    while done < n_sweeps:
+        step = min(batch, n_sweeps - done)
+        s.update_loop(step)
+        done += step
+    return s.stats()
+
+
+def _assert_verified(st, what):
+    print("%s: %.3g proposals verified; score mismatches %d, decision mismatches %d (parent sets) / %d (lambda); "
+          "screened tests redone exactly: %d / %d; margin used at most %.3f (parent sets) / %.3f (lambda); kernel %.1f s"
+          % (what, st.n_proposals, st.n_mismatch, st.n_decision_mismatch, st.n_lambda_decision_mismatch, st.n_tier1,
+             st.n_lambda_exact, st.margin_use_max, st.lambda_margin_use_max, st.kernel_ms * 1e-3))
+    assert st.n_mismatch == 0
+    assert st.n_decision_mismatch == 0 and st.n_lambda_decision_mismatch == 0
+    # a flip needs the screening error to exceed the margin: ratio > 1.  Demand headroom, not just "no flip seen".
+    assert 0.0 < st.margin_use_max < 0.5, st.margin_use_max
+    assert 0.0 < st.lambda_margin_use_max < 0.5, st.lambda_margin_use_max
+
+
+def test_decisions_verified_at_metric_point():
+    """>= 1e10 proposals at the bench's configuration (SSPS_TEST_DECISION_PROPOSALS overrides the count)."""
+    from ssps_b200 import Sampler
+    target = float(os.environ.get("SSPS_TEST_DECISION_PROPOSALS", "1e10"))
+    ds, xm, xp = make_synth(100)
+    C, V = 4096, 100
+    n_sweeps = int(np.ceil(target / (C * V) / 100.0)) * 100
+    with Sampler(large_indeg=15.0, lambda_prop_std=3.0, verify=True, psrf_grid=-1) as s:
+        s.set_data(xm, xp, ds.prior_graph)
+        st = _verified_run(s, C, n_sweeps, seed=11)
+    assert st.n_proposals == C * V * n_sweeps >= target
+    _assert_verified(st, "metric point V=100 n=28")
+
+
+def test_decisions_verified_on_c1(c1):
+    """>= 1e9 proposals on the shipped example: n = 18 < V = 46, large in-degrees, all three tiers, rank-deficient sets."""
+    from ssps_b200 import Sampler
+    target = float(os.environ.get("SSPS_TEST_DECISION_PROPOSALS_C1", "1e9"))
+    C, V = 2048, 46
+    n_sweeps = int(np.ceil(target / (C * V) / 100.0)) * 100
+    with Sampler(large_indeg=20.0, lambda_prop_std=3.0, verify=True, psrf_grid=-1) as s:
+        s.set_data(c1["Xminus"], c1["Xplus"], c1["prior"])
+        st = _verified_run(s, C, n_sweeps, seed=12)
+        raw = s.raw_stats()
+    assert st.n_proposals == C * V * n_sweeps >= target
+    assert st.n_big_steps > 0 and raw[14] > 0, "the run must visit the MID and BIG tiers"
+    _assert_verified(st, "C1 V=46 n=18")
+
+
+@pytest.fixture(scope="module")
+def synth_v1000():
+    return make_synth(1000, T=100, M=4)
+
+
+def _replay_vs_oracle(oracle, ds, xm, xp, n_chains, n_sweeps, seed, thinning=1, large_indeg=15.0):
+    from ssps_b200 import Sampler
+    V = xm.shape[1]
+    P = oracle.Problem(xm, xp, ds.prior_graph, large_indeg=large_indeg, lambda_prop_std=3.0)
+    draws = _draws(np.random.default_rng(seed), n_sweeps, n_chains, V)
+    with Sampler(large_indeg=large_indeg, lambda_prop_std=3.0, psrf_grid=-1) as s:
+        s.set_data(xm, xp, ds.prior_graph)
+        assert np.array_equal(s.gram()[0], P.G) and np.array_equal(s.gram()[1], P.R)
+        s.generate(n_chains, seed=seed)
+        s.replay(draws, thinning=thinning)
+        cnt = s.chain_edge_counts()
+        n_acc = 0
+        for c in range(n_chains):
+            ch = oracle.Chain(P, scorer=oracle.SCORER_CHOL)
+            ch.init(seed, c)
+            ch.recorder_enable()
+            for t in range(n_sweeps):
+                ch.sweep(draws[t, c])
+                if (t + 1) % thinning == 0:
+                    ch.record()
+            sets, lam, lml = s.state(c)
+            assert sets == ch.parent_sets(), "chain %d: parent sets differ" % c
+            assert np.array_equal(lam, ch.lambdas())
+            np.testing.assert_allclose(lml, ch.lmls(), rtol=1e-12)
+            assert np.array_equal(cnt[c].astype(np.int64), ch.edge_counts())
+            n_acc += ch.n_accepted
+        st = s.stats()
+        assert st.n_proposals == n_chains * V * n_sweeps
+        assert st.n_accepted == n_acc
+    return st
+
+
+def test_l2_replay_bit_exact_metric_point(oracle):
+    ds, xm, xp = make_synth(100)
+    _replay_vs_oracle(oracle, ds, xm, xp, n_chains=8, n_sweeps=40, seed=31)
+
+
+def test_l2_replay_bit_exact_c4_shape(oracle):
+    ds, xm, xp = make_synth(200, T=100, M=4)       # n = 396
+    _replay_vs_oracle(oracle, ds, xm, xp, n_chains=6, n_sweeps=20, seed=32, thinning=2)
+
+
+def test_l2_replay_bit_exact_v1000(oracle, synth_v1000):
+    ds, xm, xp = synth_v1000                        # V = 1000, n = 396, deg 1
+    _replay_vs_oracle(oracle, ds, xm, xp, n_chains=4, n_sweeps=20, seed=33)
+
+
+def test_l3_c1_posterior_vs_reference_genie_artefact(c1, c1_problem, oracle):
+    """The reference's checked-in run (4 chains x 60 s, unseeded, unconverged; scores are multiples of 1/7060) is the only
+    contact with a real reference run there is.  The converged GPU posterior must agree with it the way the oracle's own
+    chains do (measured here on the CPU: Pearson 0.84-0.87, mean edge probability 0.075-0.085 vs 0.0724, the two p = 1 edges
+    at 0.98-1.0, mean |dp| 0.033-0.035 -- chain-to-chain scatter at that length is 0.04), and with the oracle's chains far more
+    tightly.  Reported beside it: the oracle in stale-prior mode (quirk Q1, dbn_distributions.jl:102)."""
+    from concurrent.futures import ThreadPoolExecutor
+    from scipy.stats import spearmanr
+    from ssps_b200 import Sampler
+    g = c1["genie_scores"]
+    n_chains, n_sweeps = 512, 40000
+    with Sampler(large_indeg=20.0, lambda_prop_std=3.0, psrf_grid=2500) as s:
+        s.set_data(c1["Xminus"], c1["Xplus"], c1["prior"])
+        s.generate(n_chains, seed=2020)
+        s.update_loop(n_sweeps)
+        p_gpu, _, b_used, n_used = s.edge_posterior(0.5)
+        max_psrf, _ = s.psrf(0.5)
+    assert (b_used, n_used) == (n_sweeps // 2, n_sweeps)
+
+    def oracle_posterior(flags, seed):
+        def one(c):
+            ch = oracle.Chain(c1_problem, scorer=oracle.SCORER_QR, flags=flags)
+            ch.init(seed, c)
+            ch.run(4000)
+            ch.recorder_enable()
+            ch.run(4000)
+            return ch.edge_counts()
+        with ThreadPoolExecutor(8) as pool:
+            return sum(pool.map(one, range(16))) / (16 * 4000.0)
+
+    p_exact = oracle_posterior(oracle.FLAG_LML_CACHE, 5)
+    p_stale = oracle_posterior(oracle.FLAG_LML_CACHE | oracle.FLAG_STALE_PRIOR, 5)
+
+    def report(name, p):
+        r = np.corrcoef(p.ravel(), g.ravel())[0, 1]
+        rho = spearmanr(p.ravel(), g.ravel())[0]
+        print("%-28s vs genie: Pearson %.3f  Spearman %.3f  mean|dp| %.4f  mean p %.4f  MAPK->MAPK %.3f  MAPK->p90RSK %.3f"
+              % (name, r, rho, np.abs(p - g).mean(), p.mean(), p[21, 21], p[30, 21]))
+        return r, rho
+    r_gpu, rho_gpu = report("GPU exact prior (512 chains)", p_gpu)
+    report("oracle exact prior", p_exact)
+    report("oracle stale prior (Q1)", p_stale)
+    print("GPU vs oracle exact: Pearson %.4f, mean|dp| %.4f; GPU max edge PSRF %.3f; genie mean p %.4f"
+          % (np.corrcoef(p_gpu.ravel(), p_exact.ravel())[0, 1], np.abs(p_gpu - p_exact).mean(), max_psrf, g.mean()))
+    # the artefact's two certain edges (node names: MAPK -> MAPK, MAPK -> p90RSK)
+    assert p_gpu[21, 21] > 0.97 and p_gpu[30, 21] > 0.97
+    assert r_gpu > 0.8 and rho_gpu > 0.55
+    assert abs(p_gpu.mean() - g.mean()) < 0.02
+    assert np.abs(p_gpu - g).mean() < 0.045
+    # and the oracle (exact mode) is what the GPU samples: 16 x 4000 oracle samples against the converged GPU posterior
+    assert np.corrcoef(p_gpu.ravel(), p_exact.ravel())[0, 1] > 0.95
+    assert np.abs(p_gpu - p_exact).mean() < 0.03
