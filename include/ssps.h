@@ -220,6 +220,35 @@ int  ssps_changepoints_get(ssps_handle* h, int32_t chain,
                            int64_t* pe_n, int32_t* pe_child, int32_t* pe_parent, int32_t* pe_value,
                            int64_t* le_n, int32_t* le_child, double* le_value);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Multi-GPU.  Chains are independent: every handle (one per GPU) runs its own block of chain ids on its own copy of the
+ * tables; the only exchange is a SUM all-reduce of additive statistics over an NCCL communicator OWNED BY THE LIBRARY
+ * (libnccl.so.2 is resolved with dlopen when first needed; single-GPU use needs no NCCL).  Replaces the reference's
+ * offline pooling of per-chain JSON files, scripts/postprocess_samples.jl:242-259.  Two host models:
+ *   one process per GPU : rank 0 calls ssps_comm_unique_id and hands the 128 bytes to the other ranks by any host
+ *                         means (a file, MPI, torch.distributed); every rank calls ssps_comm_init_rank; the *_global
+ *                         calls are collective (every rank calls them, n = 1);
+ *   one process, n GPUs : ssps_comm_init_all on the n handles (distinct devices); ssps_run_multi keeps all GPUs busy
+ *                         from one host thread; the *_global calls take all n handles.
+ * Pass disjoint chain_id_offset blocks to ssps_init_chains: an N-GPU job then draws exactly the chains a 1-GPU job of
+ * the same total would. */
+#define SSPS_COMM_ID_BYTES 128
+int  ssps_comm_unique_id(void* id_out /* SSPS_COMM_ID_BYTES */);
+int  ssps_comm_init_rank(ssps_handle* h, int32_t n_ranks, int32_t rank, const void* id /* SSPS_COMM_ID_BYTES */);
+int  ssps_comm_init_all(ssps_handle* const* handles, int32_t n);
+int  ssps_comm_destroy(ssps_handle* h);
+int  ssps_comm_info(ssps_handle* h, int32_t* n_ranks, int32_t* rank, int32_t* nccl_version /* any may be NULL */);
+/* ssps_run on n handles at once (launches enqueued round-robin, one synchronisation at the end);
+ * *sweeps_done = the fewest sweeps any handle completed. */
+int  ssps_run_multi(ssps_handle* const* handles, int32_t n, int64_t n_sweeps, double timeout_s, int32_t thinning,
+                    int64_t* sweeps_done);
+/* ssps_psrf / ssps_edge_posterior over the chains of ALL ranks (outputs as ssps_psrf_finish / ssps_edge_posterior).
+ * Without a communicator and n = 1 they equal the local calls. */
+int  ssps_psrf_global(ssps_handle* const* handles, int32_t n, double burnin, double* max_edge_psrf,
+                      double* edge_psrf_child_major /* nullable */, double* lambda_psrf /* nullable */);
+int  ssps_edge_posterior_global(ssps_handle* const* handles, int32_t n, double burnin, double* probs_child_major,
+                                double* lambda_mean, int64_t* burnin_used, int64_t* n_used, int64_t* n_chains_total);
+
 int  ssps_get_stats(ssps_handle* h, ssps_run_stats* out);
 int  ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len);
 /* The MH kernel's raw counter block (csrc/ssps_mh.cuh, enum ST_*), for profiling builds. */

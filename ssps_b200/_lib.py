@@ -76,6 +76,14 @@ SIGNATURES = {
     "ssps_psrf": (C.c_int, [_hp, C.c_double, _dp, _dp]),
     "ssps_changepoints_size": (C.c_int, [_hp, C.c_int32, _lp, _lp]),
     "ssps_changepoints_get": (C.c_int, [_hp, C.c_int32, _lp, _ip, _ip, _ip, _lp, _ip, _dp]),
+    "ssps_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "ssps_comm_init_rank": (C.c_int, [_hp, C.c_int32, C.c_int32, C.c_void_p]),
+    "ssps_comm_init_all": (C.c_int, [C.POINTER(_hp), C.c_int32]),
+    "ssps_comm_destroy": (C.c_int, [_hp]),
+    "ssps_comm_info": (C.c_int, [_hp, _ip, _ip, _ip]),
+    "ssps_run_multi": (C.c_int, [C.POINTER(_hp), C.c_int32, C.c_int64, C.c_double, C.c_int32, _lp]),
+    "ssps_psrf_global": (C.c_int, [C.POINTER(_hp), C.c_int32, C.c_double, _dp, _dp, _dp]),
+    "ssps_edge_posterior_global": (C.c_int, [C.POINTER(_hp), C.c_int32, C.c_double, _dp, _dp, _lp, _lp, _lp]),
     "ssps_get_stats": (C.c_int, [_hp, C.POINTER(RunStats)]),
     "ssps_get_khist": (C.c_int, [_hp, _lp, C.c_int32]),
     "ssps_get_raw_stats": (C.c_int, [_hp, _lp, C.c_int32]),

@@ -25,6 +25,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <dlfcn.h>
 #include <new>
 #include <string>
 #include <unordered_map>
@@ -250,6 +251,11 @@ struct ssps_handle {
     std::vector<uint8_t> cp_present;                   // [chain][child][parent] at the last recorded sample
     std::vector<double> cp_lambda_last;                // [chain][child]
 
+    // ---- multi-GPU (NCCL communicator owned by the library; see "Multi-GPU" below) ----
+    void* comm = nullptr;           // ncclComm_t
+    int comm_rank = 0, comm_size = 1;
+    DevBuf<double> comm_buf;        // psrf sums / posterior sums staged for the all-reduce
+
     // ---- stats ----
     double kernel_ms = 0.0;
     int64_t kernel_launches = 0, mh_launches = 0;
@@ -436,10 +442,13 @@ int ssps_create(const ssps_config* cfg, ssps_handle** out) {
     return SSPS_OK;
 }
 
+int ssps_comm_destroy(ssps_handle* h);
+
 void ssps_destroy(ssps_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    if (h->comm) ssps_comm_destroy(h);
     BlockCache::get().trim(h->device);      // what earlier handles left behind goes back to the driver: the cache holds ONE footprint
     g_stream = h->stream;
     delete h;
@@ -895,115 +904,144 @@ const Snapshot* find_snapshot(const ssps_handle* h, int64_t n) {
     return nullptr;
 }
 
-// One batch of sweeps for every micro-chain.  replay_dev == nullptr => Philox streams.
-int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning, const double* replay_host,
-               int64_t* sweeps_done_out) {
+// A run = a sequence of MH launches on the handle's stream.  Split into begin / one launch / end so that ssps_run_multi can
+// keep the GPUs of several handles busy from ONE host thread (every piece only enqueues work; run_end synchronises).
+struct RunCtx {
+    int64_t n_sweeps = 0, done = 0;
+    int thinning = 1;
+    bool log_cp = false, replay = false;
+    int64_t max_rec = 0, dflt_rec = 0;
+    DevBuf<double> replay_dev;
+    size_t ev_used = 0;
+    std::chrono::steady_clock::time_point t0;
+    long long allocs0 = 0;
+};
+
+int run_begin(ssps_handle* h, RunCtx& cx, int64_t n_sweeps, int thinning, const double* replay_host) {
     if (!h->has_data || h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "ssps_run before ssps_set_data / ssps_init_chains");
     if (thinning < 1) return fail(SSPS_ERR_INVALID, "thinning must be >= 1");
     if (n_sweeps < 0 || n_sweeps % thinning != 0) return fail(SSPS_ERR_INVALID, "n_sweeps must be a non-negative multiple of thinning");
     if (h->thinning == 0) h->thinning = thinning;
     if (h->thinning != thinning) return fail(SSPS_ERR_INVALID, "thinning changed from %d to %d between runs", h->thinning, thinning);
-    const int V = h->V, C = h->n_chains;
-    const bool log_cp = h->cfg.record_changepoints != 0;
-    const int64_t max_rec = log_cp ? 4096 : 30000;          // rel indices are 15/16-bit on the device
+    cx.n_sweeps = n_sweeps; cx.done = 0; cx.thinning = thinning; cx.ev_used = 0;
+    cx.log_cp = h->cfg.record_changepoints != 0;
+    cx.replay = replay_host != nullptr;
+    cx.max_rec = cx.log_cp ? 4096 : 30000;          // rel indices are 15/16-bit on the device
+    cx.allocs0 = g_device_allocs;
+    if (cx.log_cp && h->cp_parent.empty()) CKS(changepoints_begin(h));
+    if (replay_host) CKS(upload(h, cx.replay_dev, replay_host, (size_t)n_sweeps * h->n_chains * h->V * 6));
+    cx.t0 = std::chrono::steady_clock::now();
+    return SSPS_OK;
+}
+
+// enqueue ONE launch (up to the next snapshot point)
+int run_launch(ssps_handle* h, RunCtx& cx) {
+    const int V = h->V, C = h->n_chains, thinning = cx.thinning;
     const int64_t dflt_rec = h->snap_grid > 0 ? h->snap_grid : 1024;
-    if (log_cp && h->cp_parent.empty()) CKS(changepoints_begin(h));
-
-    DevBuf<double> replay_dev;
-    if (replay_host) CKS(upload(h, replay_dev, replay_host, (size_t)n_sweeps * C * V * 6));
-
-    const auto t0 = std::chrono::steady_clock::now();
-    const long long allocs0 = g_device_allocs;
-    int64_t done = 0;
-    size_t ev_used = 0;
-    while (done < n_sweeps) {
-        if (timeout_s > 0.0) {
-            CK(cudaStreamSynchronize(h->stream));
-            const double el = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-            if (el >= timeout_s) break;
-        }
-        // launch boundary = next snapshot point (or the default batch), capped by the rel-index width
-        int64_t rec = std::min<int64_t>((n_sweeps - done) / thinning, std::min(max_rec, dflt_rec));
-        if (h->snap_grid > 0) rec = std::min(rec, h->snap_grid - h->samples_recorded % h->snap_grid);
-        // no measured task costs yet: a short calibration launch, so that the scheduler can split the heavy vertices for the rest
-        // of the batch (the first 100-sweep launch of a fresh handle ran 25 % longer than the later ones)
-        if (!h->have_cost && !replay_host && rec > 24) rec = 8;
-        const int n_local = (int)(rec * thinning);
-        MhParams prm{};
-        prm.sweep0 = h->sweeps_done; prm.n_local = n_local; prm.thinning = thinning;
-        prm.n_slabs = h->nch_pad / 32;
-        prm.n_tasks = V * prm.n_slabs;
-        prm.task_counter = h->task_counter.p;
-        prm.order = h->order.p; prm.vcost = h->vcost.p; prm.start = h->task_start.p; prm.split = h->task_split.p; prm.V = V;
-        prm.big_d = h->big_d.p; prm.big_w = h->big_w.p; prm.big_r = h->big_r.p; prm.scr_d = h->scr_d.p; prm.scr_w = h->scr_w.p; prm.scr_r = h->scr_r.p;
-        prm.x_d = h->x_d.p; prm.x_t = h->x_t.p;
-        prm.kcap = h->kcap; prm.stride = h->mh_grid * SSPS_BLOCK;
-        prm.stats = h->stats.p;
-        prm.khist = h->cfg.collect_khist ? h->khist.p : nullptr;
-        if (log_cp) {
-            CKS(changepoints_alloc(h, (int)rec, n_local));
-            prm.pev = h->pev.p; prm.pev_n = h->pev_n.p; prm.pev_cap = h->pev_cap;
-            prm.lev_val = h->lev_val.p; prm.lev_idx = h->lev_idx.p; prm.lev_n = h->lev_n.p; prm.lev_cap = h->lev_cap;
-        }
-        // task schedule: from the cycles every vertex cost in the previous launch (first launch: by in-degree, no split)
-        if (!h->have_cost) {
-            cost_from_state_kernel<<<V, 128, 0, h->stream>>>(h->st, V, h->vcost.p);
-            CKS(launch_ok(h, "cost_from_state"));
-        }
-        schedule_kernel<<<1, 256, 0, h->stream>>>(h->vcost.p, V, prm.n_slabs, h->mh_grid * (SSPS_BLOCK / 32), h->have_cost ? 1 : 0,
-                                                  h->task_split.p, h->order.p, h->task_start.p, h->task_est.p);
-        CKS(launch_ok(h, "order"));
-        CK(cudaMemsetAsync(h->vcost.p, 0, h->vcost.bytes(), h->stream));
-        h->have_cost = true;
-        CK(cudaMemsetAsync(h->task_counter.p, 0, sizeof(int), h->stream));
-        if (ev_used == h->ev_pool.size()) {
-            cudaEvent_t a, b;
-            CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
-            h->ev_pool.emplace_back(a, b);
-        }
-        CK(cudaEventRecord(h->ev_pool[ev_used].first, h->stream));
-        if (h->is_poly) {
-            if (replay_host) {
-                ReplaySource src{replay_dev.p + (size_t)done * C * V * 6, C, V};
-                mh_poly_kernel<ReplaySource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p);
-            } else {
-                PhiloxSource src{h->seed, h->chain_offset};
-                mh_poly_kernel<PhiloxSource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p);
-            }
-        } else if (replay_host) {
-            ReplaySource src{replay_dev.p + (size_t)done * C * V * 6, C, V};
-            if (h->cfg.verify) mh_sweeps_kernel<ReplaySource, true><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
-            else mh_sweeps_kernel<ReplaySource, false><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+    // launch boundary = next snapshot point (or the default batch), capped by the rel-index width
+    int64_t rec = std::min<int64_t>((cx.n_sweeps - cx.done) / thinning, std::min(cx.max_rec, dflt_rec));
+    if (h->snap_grid > 0) rec = std::min(rec, h->snap_grid - h->samples_recorded % h->snap_grid);
+    // no measured task costs yet: a short calibration launch, so that the scheduler can split the heavy vertices for the rest
+    // of the batch (the first 100-sweep launch of a fresh handle ran 25 % longer than the later ones)
+    if (!h->have_cost && !cx.replay && rec > 24) rec = 8;
+    const int n_local = (int)(rec * thinning);
+    MhParams prm{};
+    prm.sweep0 = h->sweeps_done; prm.n_local = n_local; prm.thinning = thinning;
+    prm.n_slabs = h->nch_pad / 32;
+    prm.n_tasks = V * prm.n_slabs;
+    prm.task_counter = h->task_counter.p;
+    prm.order = h->order.p; prm.vcost = h->vcost.p; prm.start = h->task_start.p; prm.split = h->task_split.p; prm.V = V;
+    prm.big_d = h->big_d.p; prm.big_w = h->big_w.p; prm.big_r = h->big_r.p; prm.scr_d = h->scr_d.p; prm.scr_w = h->scr_w.p; prm.scr_r = h->scr_r.p;
+    prm.x_d = h->x_d.p; prm.x_t = h->x_t.p;
+    prm.kcap = h->kcap; prm.stride = h->mh_grid * SSPS_BLOCK;
+    prm.stats = h->stats.p;
+    prm.khist = h->cfg.collect_khist ? h->khist.p : nullptr;
+    if (cx.log_cp) {
+        CKS(changepoints_alloc(h, (int)rec, n_local));
+        prm.pev = h->pev.p; prm.pev_n = h->pev_n.p; prm.pev_cap = h->pev_cap;
+        prm.lev_val = h->lev_val.p; prm.lev_idx = h->lev_idx.p; prm.lev_n = h->lev_n.p; prm.lev_cap = h->lev_cap;
+    }
+    // task schedule: from the cycles every vertex cost in the previous launch (first launch: by in-degree, no split)
+    if (!h->have_cost) {
+        cost_from_state_kernel<<<V, 128, 0, h->stream>>>(h->st, V, h->vcost.p);
+        CKS(launch_ok(h, "cost_from_state"));
+    }
+    schedule_kernel<<<1, 256, 0, h->stream>>>(h->vcost.p, V, prm.n_slabs, h->mh_grid * (SSPS_BLOCK / 32), h->have_cost ? 1 : 0,
+                                              h->task_split.p, h->order.p, h->task_start.p, h->task_est.p);
+    CKS(launch_ok(h, "order"));
+    CK(cudaMemsetAsync(h->vcost.p, 0, h->vcost.bytes(), h->stream));
+    h->have_cost = true;
+    CK(cudaMemsetAsync(h->task_counter.p, 0, sizeof(int), h->stream));
+    if (cx.ev_used == h->ev_pool.size()) {
+        cudaEvent_t a, b;
+        CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+        h->ev_pool.emplace_back(a, b);
+    }
+    CK(cudaEventRecord(h->ev_pool[cx.ev_used].first, h->stream));
+    const double* rp = cx.replay ? cx.replay_dev.p + (size_t)cx.done * C * V * 6 : nullptr;
+    if (h->is_poly) {
+        if (cx.replay) {
+            ReplaySource src{rp, C, V};
+            mh_poly_kernel<ReplaySource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p);
         } else {
             PhiloxSource src{h->seed, h->chain_offset};
-            if (h->cfg.verify) mh_sweeps_kernel<PhiloxSource, true><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
-            else mh_sweeps_kernel<PhiloxSource, false><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+            mh_poly_kernel<PhiloxSource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p);
         }
-        CKS(launch_ok(h, "mh_sweeps_kernel"));
-        CK(cudaEventRecord(h->ev_pool[ev_used].second, h->stream));
-        ++ev_used; ++h->mh_launches;
-        const int64_t rec_base = h->samples_recorded;
-        h->sweeps_done += n_local; h->samples_recorded += rec; done += n_local;
-        if (log_cp) CKS(changepoints_drain(h, rec_base));
-        CKS(take_snapshot(h));
-        if (ev_used >= 256) {   // resolve timings in bounded batches
-            CK(cudaStreamSynchronize(h->stream));
-            for (size_t e = 0; e < ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
-            ev_used = 0;
-        }
+    } else if (cx.replay) {
+        ReplaySource src{rp, C, V};
+        if (h->cfg.verify) mh_sweeps_kernel<ReplaySource, true><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+        else mh_sweeps_kernel<ReplaySource, false><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+    } else {
+        PhiloxSource src{h->seed, h->chain_offset};
+        if (h->cfg.verify) mh_sweeps_kernel<PhiloxSource, true><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
+        else mh_sweeps_kernel<PhiloxSource, false><<<h->mh_grid, SSPS_BLOCK, h->mh_smem, h->stream>>>(h->dev, h->st, prm, src);
     }
+    CKS(launch_ok(h, "mh_sweeps_kernel"));
+    CK(cudaEventRecord(h->ev_pool[cx.ev_used].second, h->stream));
+    ++cx.ev_used; ++h->mh_launches;
+    const int64_t rec_base = h->samples_recorded;
+    h->sweeps_done += n_local; h->samples_recorded += rec; cx.done += n_local;
+    if (cx.log_cp) CKS(changepoints_drain(h, rec_base));
+    CKS(take_snapshot(h));
+    if (cx.ev_used >= 256) {   // resolve timings in bounded batches
+        CK(cudaStreamSynchronize(h->stream));
+        for (size_t e = 0; e < cx.ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
+        cx.ev_used = 0;
+    }
+    return SSPS_OK;
+}
+
+int run_end(ssps_handle* h, RunCtx& cx, int64_t* sweeps_done_out) {
     CK(cudaStreamSynchronize(h->stream));
     if (getenv("SSPS_TRACE")) {
-        const double ms = 1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-        float kms = 0; for (size_t e = 0; e < ev_used; ++e) { float m1 = 0; cudaEventElapsedTime(&m1, h->ev_pool[e].first, h->ev_pool[e].second); kms += m1;
+        const double ms = 1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - cx.t0).count();
+        float kms = 0; for (size_t e = 0; e < cx.ev_used; ++e) { float m1 = 0; cudaEventElapsedTime(&m1, h->ev_pool[e].first, h->ev_pool[e].second); kms += m1;
             if (atoi(getenv("SSPS_TRACE")) >= 2) fprintf(stderr, "[ssps trace] launch %zu: %.2f ms\n", e, m1); }
-        if (ms > 1.5 * kms + 2.0) fprintf(stderr, "[ssps trace] run_sweeps %.1f ms wall, %.1f ms in the MH kernel (%lld sweeps)\n", ms, kms, (long long)done);
+        if (ms > 1.5 * kms + 2.0) fprintf(stderr, "[ssps trace] run_sweeps %.1f ms wall, %.1f ms in the MH kernel (%lld sweeps)\n", ms, kms, (long long)cx.done);
     }
-    for (size_t e = 0; e < ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
-    if (sweeps_done_out) *sweeps_done_out = done;
-    h->allocs_in_run += g_device_allocs - allocs0;
+    for (size_t e = 0; e < cx.ev_used; ++e) { float ms = 0; CK(cudaEventElapsedTime(&ms, h->ev_pool[e].first, h->ev_pool[e].second)); h->kernel_ms += ms; }
+    cx.ev_used = 0;
+    if (sweeps_done_out) *sweeps_done_out = cx.done;
+    h->allocs_in_run += g_device_allocs - cx.allocs0;
+    cx.replay_dev.release();
     // (a proposal that would exceed max_indegree is rejected and counted -- ST_KCAP_REJECT -- never an error after the fact)
     return SSPS_OK;
+}
+
+// One batch of sweeps for every micro-chain.  replay_host == nullptr => Philox streams.
+int run_sweeps(ssps_handle* h, int64_t n_sweeps, double timeout_s, int thinning, const double* replay_host,
+               int64_t* sweeps_done_out) {
+    RunCtx cx;
+    CKS(run_begin(h, cx, n_sweeps, thinning, replay_host));
+    while (cx.done < cx.n_sweeps) {
+        if (timeout_s > 0.0) {
+            CK(cudaStreamSynchronize(h->stream));
+            const double el = std::chrono::duration<double>(std::chrono::steady_clock::now() - cx.t0).count();
+            if (el >= timeout_s) break;
+        }
+        CKS(run_launch(h, cx));
+    }
+    return run_end(h, cx, sweeps_done_out);
 }
 
 }  // namespace
@@ -1483,6 +1521,321 @@ int ssps_measure_fp64_peak(ssps_handle* h, double* tflops) {
     }
     cudaEventDestroy(a); cudaEventDestroy(b);
     *tflops = best;
+    return SSPS_OK;
+}
+
+}  // extern "C"
+
+// ================================================================================================
+// Multi-GPU: chains are sharded over handles (one per GPU, in one process or one process per GPU); the only
+// exchange is a SUM all-reduce of additive statistics -- the split-PSRF sums of ssps_psrf_sums and the pooled
+// tallies of ssps_edge_posterior -- over an NCCL communicator the LIBRARY owns.  It replaces the
+// reference's offline pooling of per-chain JSON files (scripts/postprocess_samples.jl:242-259).
+// libnccl.so.2 is resolved at run time (dlopen): single-GPU users need no NCCL at all, and inside a torch process the
+// copy torch already loaded is the one that is used.
+// ================================================================================================
+namespace {
+
+struct NcclId { char internal[128]; };      // == ncclUniqueId (nccl.h)
+typedef void* NcclComm;                     // == ncclComm_t
+enum { NCCL_FLOAT64 = 8, NCCL_SUM = 0, NCCL_MAX = 2 };      // ncclDataType_t / ncclRedOp_t values (nccl.h)
+
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(NcclId*) = nullptr;
+    int (*CommInitRank)(NcclComm*, int, NcclId, int) = nullptr;
+    int (*CommDestroy)(NcclComm) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    int (*GetVersion)(int*) = nullptr;
+};
+
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);      // the copy this process already has (torch's), if any
+        if (!lib) if (const char* e = getenv("SSPS_NCCL_LIB")) lib = dlopen(e, RTLD_NOW);
+        if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW);
+        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW);
+        if (!lib) return;
+        api.lib = lib;
+        *(void**)&api.GetUniqueId = dlsym(lib, "ncclGetUniqueId");
+        *(void**)&api.CommInitRank = dlsym(lib, "ncclCommInitRank");
+        *(void**)&api.CommDestroy = dlsym(lib, "ncclCommDestroy");
+        *(void**)&api.AllReduce = dlsym(lib, "ncclAllReduce");
+        *(void**)&api.GroupStart = dlsym(lib, "ncclGroupStart");
+        *(void**)&api.GroupEnd = dlsym(lib, "ncclGroupEnd");
+        *(void**)&api.GetErrorString = dlsym(lib, "ncclGetErrorString");
+        *(void**)&api.GetVersion = dlsym(lib, "ncclGetVersion");
+    });
+    if (!api.lib || !api.GetUniqueId || !api.CommInitRank || !api.CommDestroy || !api.AllReduce || !api.GroupStart || !api.GroupEnd) return nullptr;
+    return &api;
+}
+
+int need_nccl(NcclApi*& api) {
+    api = nccl_api();
+    if (!api) return fail(SSPS_ERR_UNAVAILABLE, "libnccl.so.2 could not be loaded (%s); set SSPS_NCCL_LIB or LD_LIBRARY_PATH", dlerror() ? dlerror() : "symbols missing");
+    return SSPS_OK;
+}
+
+#define NK(api, call)                                                                                          \
+    do {                                                                                                       \
+        int r_ = (call);                                                                                       \
+        if (r_ != 0) return fail(SSPS_ERR_CUDA, "%s: %s", #call, (api)->GetErrorString ? (api)->GetErrorString(r_) : "nccl error"); \
+    } while (0)
+
+// un-normalised pooled tallies of the local chains on the device: out[0 .. V*V) = sum over chains of post-burn-in counts,
+// out[V*V .. +V) = the same for lambda, out[V*V + V] = (n - b) * local chains
+int posterior_sums(ssps_handle* h, double burnin, double* out_dev, int64_t* b_out, int64_t* n_out) {
+    if (h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "no chains");
+    if (!(burnin >= 0.0 && burnin < 1.0)) return fail(SSPS_ERR_INVALID, "burnin must be in [0, 1)");
+    const int64_t n = h->samples_recorded;
+    if (n < 1) return fail(SSPS_ERR_UNAVAILABLE, "no recorded samples yet");
+    const int64_t want = (int64_t)floor(burnin * (double)n);   // postprocess_samples.jl:186
+    const Snapshot* lo = nullptr;
+    for (const auto& sn : h->snaps)
+        if (sn.n <= want && sn.n < n && (!lo || sn.n > lo->n)) lo = &sn;
+    const int64_t b = lo ? lo->n : 0;
+    const size_t vv = (size_t)h->V * h->V;
+    int chunks = 1, chunk_len = h->n_chains;
+    chain_chunks(h, vv, chunks, chunk_len);
+    CK(cudaMemsetAsync(out_dev, 0, (vv + (size_t)h->V + 1) * sizeof(double), h->stream));
+    edge_sum_kernel<<<dim3(div_up(vv, 256), chunks), 256, 0, h->stream>>>(h->counts.p, lo ? lo->counts : nullptr, h->n_chains, vv, chunk_len, out_dev);
+    CKS(launch_ok(h, "edge_sum"));
+    lam_sum_kernel<<<h->V, 256, 0, h->stream>>>(h->lam_sum.p, lo ? lo->lam_sum : nullptr, h->n_chains, h->V, out_dev + vv);
+    CKS(launch_ok(h, "lam_sum"));
+    const double denom = (double)(n - b) * (double)h->n_chains;
+    CK(cudaMemcpyAsync(out_dev + vv + h->V, &denom, sizeof denom, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));       // `denom` is a stack variable
+    if (b_out) *b_out = b;
+    if (n_out) *n_out = n;
+    return SSPS_OK;
+}
+
+// SUM all-reduce of `count` doubles staged in every handle's comm_buf (in place); one group call for all local handles
+int comm_allreduce(ssps_handle* const* hs, int n, size_t count, int op) {
+    NcclApi* api = nullptr;
+    bool any = false;
+    for (int e = 0; e < n; ++e) any = any || hs[e]->comm != nullptr;
+    if (!any) {
+        if (n == 1) return SSPS_OK;             // a single handle without a communicator: the local sums are the global ones
+        return fail(SSPS_ERR_INVALID, "%d handles but no communicator: call ssps_comm_init_all first", n);
+    }
+    CKS(need_nccl(api));
+    NK(api, api->GroupStart());
+    for (int e = 0; e < n; ++e) {
+        ssps_handle* h = hs[e];
+        if (!h->comm) { api->GroupEnd(); return fail(SSPS_ERR_INVALID, "handle %d has no communicator", e); }
+        CK(cudaSetDevice(h->device));
+        NK(api, api->AllReduce(h->comm_buf.p, h->comm_buf.p, count, NCCL_FLOAT64, op, h->comm, h->stream));
+    }
+    NK(api, api->GroupEnd());
+    for (int e = 0; e < n; ++e) { CK(cudaSetDevice(hs[e]->device)); CK(cudaStreamSynchronize(hs[e]->stream)); }
+    return SSPS_OK;
+}
+
+int check_handles(ssps_handle* const* hs, int n) {
+    if (!hs || n < 1) return fail(SSPS_ERR_INVALID, "need at least one handle");
+    for (int e = 0; e < n; ++e) {
+        if (!hs[e]) return fail(SSPS_ERR_INVALID, "handle %d is null", e);
+        if (hs[e]->V != hs[0]->V) return fail(SSPS_ERR_INVALID, "handle %d holds a different data set (V=%d vs %d)", e, hs[e]->V, hs[0]->V);
+    }
+    return SSPS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ssps_comm_unique_id(void* id_out) {
+    if (!id_out) return fail(SSPS_ERR_INVALID, "null id buffer");
+    NcclApi* api = nullptr;
+    CKS(need_nccl(api));
+    NcclId id;
+    NK(api, api->GetUniqueId(&id));
+    memcpy(id_out, &id, sizeof id);
+    return SSPS_OK;
+}
+
+int ssps_comm_init_rank(ssps_handle* h, int32_t n_ranks, int32_t rank, const void* id) {
+    CKS(bind(h));
+    if (!id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(SSPS_ERR_INVALID, "ssps_comm_init_rank: bad argument");
+    if (h->comm) return fail(SSPS_ERR_INVALID, "the handle already has a communicator");
+    NcclApi* api = nullptr;
+    CKS(need_nccl(api));
+    NcclId nid;
+    memcpy(&nid, id, sizeof nid);
+    NcclComm c = nullptr;
+    NK(api, api->CommInitRank(&c, n_ranks, nid, rank));
+    h->comm = c; h->comm_rank = rank; h->comm_size = n_ranks;
+    return SSPS_OK;
+}
+
+int ssps_comm_init_all(ssps_handle* const* hs, int32_t n) {
+    CKS(check_handles(hs, n));
+    NcclApi* api = nullptr;
+    CKS(need_nccl(api));
+    for (int e = 0; e < n; ++e) {
+        if (hs[e]->comm) return fail(SSPS_ERR_INVALID, "handle %d already has a communicator", e);
+        for (int f = 0; f < e; ++f) if (hs[f]->device == hs[e]->device) return fail(SSPS_ERR_INVALID, "handles %d and %d share device %d", f, e, hs[e]->device);
+    }
+    NcclId id;
+    NK(api, api->GetUniqueId(&id));
+    std::vector<NcclComm> comms((size_t)n, nullptr);
+    NK(api, api->GroupStart());
+    for (int e = 0; e < n; ++e) {
+        CK(cudaSetDevice(hs[e]->device));
+        NK(api, api->CommInitRank(&comms[e], n, id, e));
+    }
+    NK(api, api->GroupEnd());
+    for (int e = 0; e < n; ++e) { hs[e]->comm = comms[e]; hs[e]->comm_rank = e; hs[e]->comm_size = n; }
+    return SSPS_OK;
+}
+
+int ssps_comm_destroy(ssps_handle* h) {
+    CKS(bind(h));
+    if (!h->comm) return SSPS_OK;
+    NcclApi* api = nullptr;
+    CKS(need_nccl(api));
+    CK(cudaStreamSynchronize(h->stream));
+    NK(api, api->CommDestroy(h->comm));
+    h->comm = nullptr; h->comm_rank = 0; h->comm_size = 1;
+    return SSPS_OK;
+}
+
+int ssps_comm_info(ssps_handle* h, int32_t* n_ranks, int32_t* rank, int32_t* nccl_version) {
+    if (!h) return fail(SSPS_ERR_INVALID, "null handle");
+    if (n_ranks) *n_ranks = h->comm ? h->comm_size : 1;
+    if (rank) *rank = h->comm ? h->comm_rank : 0;
+    if (nccl_version) {
+        *nccl_version = 0;
+        NcclApi* api = nccl_api();
+        if (api && api->GetVersion) api->GetVersion(nccl_version);
+    }
+    return SSPS_OK;
+}
+
+// ssps_run on every handle at once: one host thread keeps all GPUs busy (launches are enqueued round-robin, one
+// synchronisation at the end; with a timeout, one check per round of launches)
+int ssps_run_multi(ssps_handle* const* hs, int32_t n, int64_t n_sweeps, double timeout_s, int32_t thinning, int64_t* sweeps_done) {
+    CKS(check_handles(hs, n));
+    std::vector<RunCtx> cx((size_t)n);
+    for (int e = 0; e < n; ++e) { CKS(bind(hs[e])); CKS(run_begin(hs[e], cx[e], n_sweeps, thinning, nullptr)); }
+    const auto t0 = std::chrono::steady_clock::now();
+    for (;;) {
+        bool left = false;
+        for (int e = 0; e < n; ++e) left = left || cx[e].done < cx[e].n_sweeps;
+        if (!left) break;
+        if (timeout_s > 0.0) {
+            for (int e = 0; e < n; ++e) { CK(cudaSetDevice(hs[e]->device)); CK(cudaStreamSynchronize(hs[e]->stream)); }
+            if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() >= timeout_s) break;
+        }
+        for (int e = 0; e < n; ++e)
+            if (cx[e].done < cx[e].n_sweeps) { CKS(bind(hs[e])); CKS(run_launch(hs[e], cx[e])); }
+    }
+    int64_t done_min = n_sweeps;
+    for (int e = 0; e < n; ++e) {
+        int64_t d = 0;
+        CKS(bind(hs[e]));
+        CKS(run_end(hs[e], cx[e], &d));
+        done_min = std::min(done_min, d);
+    }
+    if (sweeps_done) *sweeps_done = done_min;
+    return SSPS_OK;
+}
+
+// split-PSRF over the chains of ALL ranks.  hs = the handles this process drives: n = 1 in the process-per-GPU model
+// (collective: every rank calls it), all local handles after ssps_comm_init_all.  Outputs as ssps_psrf_finish.
+int ssps_psrf_global(ssps_handle* const* hs, int32_t n, double burnin, double* max_edge_psrf, double* edge_psrf_child_major,
+                     double* lambda_psrf) {
+    CKS(check_handles(hs, n));
+    const size_t total = (size_t)ssps_psrf_sums_len(hs[0]->V);
+    // every rank must split its chains at the same samples: exchange (L, -L) with MAX first
+    int first_err = SSPS_OK;
+    std::string first_msg;
+    for (int e = 0; e < n; ++e) {
+        CKS(bind(hs[e]));
+        CK(hs[e]->comm_buf.alloc(total + 2));
+        int rc = ssps_psrf_sums(hs[e], burnin, hs[e]->comm_buf.p, 1);
+        if (rc != SSPS_OK && first_err == SSPS_OK) { first_err = rc; first_msg = g_err; }
+        // length used = tail[1] / tail[0] * 2 + b ... carried explicitly instead: the half length n1 identifies the triple
+        double chk[2] = {-1.0, -1.0};
+        if (rc == SSPS_OK) {
+            double tail[2];
+            CK(cudaMemcpyAsync(tail, hs[e]->comm_buf.p + total - 2, sizeof tail, cudaMemcpyDeviceToHost, hs[e]->stream));
+            CK(cudaStreamSynchronize(hs[e]->stream));
+            chk[0] = tail[1] / tail[0]; chk[1] = -chk[0];
+        } else {
+            CK(cudaMemsetAsync(hs[e]->comm_buf.p, 0, total * sizeof(double), hs[e]->stream));
+            chk[0] = 1e300; chk[1] = 1e300;        // poisons the agreement test on every rank
+        }
+        CK(cudaMemcpyAsync(hs[e]->comm_buf.p + total, chk, sizeof chk, cudaMemcpyHostToDevice, hs[e]->stream));
+        CK(cudaStreamSynchronize(hs[e]->stream));
+    }
+    // two all-reduces: the check words with MAX, then the sums with SUM (both tiny: latency-bound over NVLink)
+    {
+        std::vector<DevBuf<double>> tmp((size_t)n);
+        bool any = false;
+        for (int e = 0; e < n; ++e) any = any || hs[e]->comm != nullptr;
+        if (any) {
+            NcclApi* api = nullptr;
+            CKS(need_nccl(api));
+            NK(api, api->GroupStart());
+            for (int e = 0; e < n; ++e) {
+                if (!hs[e]->comm) { api->GroupEnd(); return fail(SSPS_ERR_INVALID, "handle %d has no communicator", e); }
+                CK(cudaSetDevice(hs[e]->device));
+                NK(api, api->AllReduce(hs[e]->comm_buf.p + total, hs[e]->comm_buf.p + total, 2, NCCL_FLOAT64, NCCL_MAX, hs[e]->comm, hs[e]->stream));
+            }
+            NK(api, api->GroupEnd());
+        } else if (n > 1) return fail(SSPS_ERR_INVALID, "%d handles but no communicator: call ssps_comm_init_all first", n);
+    }
+    for (int e = 0; e < n; ++e) {
+        double chk[2];
+        CK(cudaSetDevice(hs[e]->device));
+        CK(cudaMemcpyAsync(chk, hs[e]->comm_buf.p + total, sizeof chk, cudaMemcpyDeviceToHost, hs[e]->stream));
+        CK(cudaStreamSynchronize(hs[e]->stream));
+        if (chk[0] >= 1e300) {
+            if (first_err != SSPS_OK) { g_err = first_msg; return first_err; }
+            return fail(SSPS_ERR_UNAVAILABLE, "another rank has no snapshot-aligned (burn-in, split, length) triple yet");
+        }
+        if (chk[0] != -chk[1])
+            return fail(SSPS_ERR_UNAVAILABLE, "ranks would split their chains at different samples (half lengths %g..%g): run the same "
+                        "number of sweeps with the same psrf_grid / snapshot_slots on every rank", -chk[1], chk[0]);
+    }
+    CKS(comm_allreduce(hs, n, total, NCCL_SUM));
+    CKS(bind(hs[0]));
+    return ssps_psrf_finish(hs[0], hs[0]->comm_buf.p, 1, max_edge_psrf, edge_psrf_child_major, lambda_psrf);
+}
+
+// evaluate_summary over the chains of ALL ranks (postprocess_samples.jl:183-191)
+int ssps_edge_posterior_global(ssps_handle* const* hs, int32_t n, double burnin, double* probs_child_major, double* lambda_mean,
+                               int64_t* burnin_used, int64_t* n_used, int64_t* n_chains_total) {
+    CKS(check_handles(hs, n));
+    const int V = hs[0]->V;
+    const size_t vv = (size_t)V * V, total = vv + (size_t)V + 1;
+    int64_t b0 = 0, n0 = 0;
+    for (int e = 0; e < n; ++e) {
+        int64_t b = 0, nn = 0;
+        CKS(bind(hs[e]));
+        CK(hs[e]->comm_buf.alloc((size_t)ssps_psrf_sums_len(V) + 2));
+        CKS(posterior_sums(hs[e], burnin, hs[e]->comm_buf.p, &b, &nn));
+        if (e == 0) { b0 = b; n0 = nn; }
+        else if (b != b0 || nn != n0) return fail(SSPS_ERR_INVALID, "handles %d and 0 are at different samples (%lld/%lld vs %lld/%lld)", e, (long long)b, (long long)nn, (long long)b0, (long long)n0);
+    }
+    CKS(comm_allreduce(hs, n, total, NCCL_SUM));
+    CKS(bind(hs[0]));
+    std::vector<double> host(total);
+    CKS(download(hs[0], host.data(), hs[0]->comm_buf.p, total));
+    CK(cudaStreamSynchronize(hs[0]->stream));
+    const double denom = host[vv + V];
+    if (probs_child_major) for (size_t e = 0; e < vv; ++e) probs_child_major[e] = host[e] / denom;
+    if (lambda_mean) for (int i = 0; i < V; ++i) lambda_mean[i] = host[vv + i] / denom;
+    if (burnin_used) *burnin_used = b0;
+    if (n_used) *n_used = n0;
+    if (n_chains_total) *n_chains_total = (int64_t)llround(denom / (double)(n0 - b0));
     return SSPS_OK;
 }
 

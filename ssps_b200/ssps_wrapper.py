@@ -8,7 +8,10 @@ sampling itself runs in libssps_b200.so on one B200; there is no CPU path.
 
 Extensions (not in the reference): --n-chains K writes K chains from one process
 (<output> gets the first chain, or use a `{chain}` placeholder in the output path); --seed;
---device; --posterior-json writes the pooled postprocess_samples.jl-style summary directly.
+--device; --gpus N shards the K chains over N GPUs of the box (one process, ssps_run_multi; the
+pooled statistics are all-reduced by the library's own NCCL communicator); --posterior-json writes
+the pooled postprocess_samples.jl-style summary directly; --no-chain-json skips the per-chain files
+(thousands of chains).
 """
 from __future__ import annotations
 
@@ -51,6 +54,8 @@ def parse_script_arguments(argv=None) -> argparse.Namespace:
     p.add_argument("--n-chains", type=int, default=1)
     p.add_argument("--seed", type=int, default=None)
     p.add_argument("--device", type=int, default=-1)
+    p.add_argument("--gpus", type=int, default=1, help="shard --n-chains over this many GPUs of the box (devices 0..N-1)")
+    p.add_argument("--no-chain-json", action="store_true", help="do not write the per-chain change-point JSON files")
     p.add_argument("--posterior-json", default="", help="also write the pooled edge posterior / PSRF summary here")
     p.add_argument("--burnin", type=float, default=0.5)
     return p.parse_args(argv)
@@ -67,7 +72,8 @@ def recover_state(samples: dict):
 
 def perform_inference(timeseries_filename, ref_graph_filename, output_path, timeout, n_steps, thinning,
                       large_indeg, lambda_max, regression_deg, lambda_prop_std, proposal, resume_sampling,
-                      multithread, n_chains=1, seed=None, device=-1, posterior_json="", burnin=0.5):
+                      multithread, n_chains=1, seed=None, device=-1, posterior_json="", burnin=0.5, gpus=1,
+                      no_chain_json=False):
     """perform_inference (SSPS.jl:135-233)."""
     if proposal == "uniform" and not multithread:
         raise SystemExit("--proposal uniform (deprecated in the reference, SSPS.jl:88) is not implemented")
@@ -78,16 +84,29 @@ def perform_inference(timeseries_filename, ref_graph_filename, output_path, time
     series, prior, _ = load_formatted_data(timeseries_filename, ref_graph_filename)
     print("Invoking SSPS on input files:\n\t%s\n\t%s" % (timeseries_filename, ref_graph_filename))
     t_start = time.time()
-    smp = Sampler(device=device, regression_deg=regression_deg, large_indeg=large_indeg, lambda_max=lambda_max,
-                  lambda_prop_std=lambda_prop_std, record_changepoints=True)
-    smp.set_timeseries(series, prior)
+    kw = dict(regression_deg=regression_deg, large_indeg=large_indeg, lambda_max=lambda_max,
+              lambda_prop_std=lambda_prop_std, record_changepoints=not no_chain_json)
     if seed is None:
         seed = int(time.time_ns() & 0x7FFFFFFFFFFFFFFF)   # the reference never seeds its RNG either
+    multi = gpus > 1
+    if multi:
+        from .multi_gpu import MultiGpuSampler
+        if n_chains < gpus:
+            raise SystemExit("--gpus %d needs at least that many chains (--n-chains %d)" % (gpus, n_chains))
+        smp = MultiGpuSampler(n_chains, list(range(gpus)), seed=seed, **kw)
+    else:
+        smp = Sampler(device=device, **kw)
+    smp.set_timeseries(series, prior)
+    init_sets = init_lam = None
     if resume_sampling:
         print("Resuming Markov Chain stored at", resume_sampling)
         with open(resume_sampling) as f:
             psets, lam = recover_state(json.load(f))
-        smp.generate(n_chains, seed=seed, init_parent_sets=[psets] * n_chains, init_lambda=[lam] * n_chains)
+        init_sets, init_lam = [psets] * n_chains, [lam] * n_chains
+    if multi:
+        smp.generate(init_parent_sets=init_sets, init_lambda=init_lam)
+    elif init_sets is not None:
+        smp.generate(n_chains, seed=seed, init_parent_sets=init_sets, init_lambda=init_lam)
     else:
         smp.generate(n_chains, seed=seed)
 
@@ -111,7 +130,7 @@ def perform_inference(timeseries_filename, ref_graph_filename, output_path, time
     t_elapsed = time.time() - t_start
 
     print("Saving results to JSON file:")
-    for c in range(n_chains):
+    for c in range(n_chains if not no_chain_json else 0):
         path = output_path.replace("{chain}", str(c)) if "{chain}" in output_path else (
             output_path if c == 0 else "%s.chain%d" % (output_path, c))
         with open(path, "w") as f:
@@ -131,7 +150,8 @@ def main(argv=None) -> int:
     return perform_inference(a.timeseries_filename, a.ref_graph_filename, a.output_path, a.timeout, a.n_steps,
                              a.thinning, a.large_indeg, a.lambda_max, a.regression_deg, a.lambda_prop_std,
                              a.proposal, a.resume_sampling, a.multithread, n_chains=a.n_chains, seed=a.seed,
-                             device=a.device, posterior_json=a.posterior_json, burnin=a.burnin)
+                             device=a.device, posterior_json=a.posterior_json, burnin=a.burnin, gpus=a.gpus,
+                             no_chain_json=a.no_chain_json)
 
 
 if __name__ == "__main__":
