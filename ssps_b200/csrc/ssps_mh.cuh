@@ -940,10 +940,17 @@ __device__ __forceinline__ void tri_decode(const int idx, int& u, int& v) {
 // The trailing triangle is spread over the lanes pair by pair (a, c), c <= a, numbered from the LAST row
 // upwards, so that the pairs still alive at step b are always a prefix of the lane's list.
 __device__ __noinline__ double fac_remove(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int k, const int p,
-                                          double q, const int lane) {
+                                          double q, const int lane
+#ifdef SSPS_PROFILE_BIG
+                                          , unsigned long long* prof
+#endif
+                                          ) {
     const int V = P.V, kr = k - 1, nt = kr - p;
     double* t = T.t; double* tw = T.tw;
     if (nt <= 0) return q;
+#ifdef SSPS_PROFILE_BIG
+    const long long tp0_ = clock64();
+#endif
 #define SROW(a) (t + SSPS_TRI((a) + 1))      /* a >= p: stage row a + 1 */
 #define SCOL(c) ((c) + 1)                    /* c >= p: stage column c + 1 */
     // partial sums over the unchanged columns m < p; the diagonal pair of row a also carries t_a
@@ -965,33 +972,63 @@ __device__ __noinline__ double fac_remove(const SspsDev& P, const double* __rest
         ra[SCOL(c)] = x;
     }
     __syncwarp();
-    // Trailing update, a lane per row (rows a = p + lane, + 32, ...): once column b is final, lane a scales its entry of
-    // that column and subtracts its products from the entries (a, c), b < c <= a, of its own row.  Every entry still
-    // receives its terms in ascending b through fma -- the bits of the row-by-row factorisation.  (The pair-per-lane
-    // form of the first version spent more on decoding pair numbers than on the fma they led to.)
+    // Trailing update, a lane per row (lane owns rows a = p + lane, + 32, ...).  Step b: every lane forms the pivot (1 / d_b, w_b)
+    // from d_b^2 and t_b, which the owner of row b handed to the warp by shuffle at the end of the previous step -- so the
+    // dependent chain from one pivot to the next is  1/sqrt -> one multiply -> one fma -> shuffle  and nothing else; then lane a
+    // scales its entry of column b and subtracts its products from the entries (a, c), b < c <= a, of its own row, reading the
+    // still UNSCALED column b of the other rows (x * inv gives the bits the owner will store).  Every entry receives its terms in
+    // ascending b through fma -- the bits of the row-by-row factorisation.  ONE warp barrier per step: the scaled column goes
+    // to shared memory after it, when nobody reads the unscaled one any more.  (Round 1: three barriers per step and the pivot read
+    // back from shared memory, 700 cycles per step; 65 % of a BIG-tier pass was spent here.)
+#ifdef SSPS_PROFILE_BIG
+    const long long tp1_ = clock64();
+#endif
     double gd = 0.0;                                    // G_aa of this lane's first row: the pivots' tolerance reference
     if (p + lane < kr) { const int ja = T.idof(p + lane); gd = __ldg(P.G + (size_t)ja * V + ja); }
+    double d2 = SROW(p)[SCOL(p)], tb = tw[p + 1];
     for (int b = p; b < kr; ++b) {
-        double* rb = SROW(b);
-        const double d2 = rb[SCOL(b)], tb = tw[b + 1];
         double gbb = __shfl_sync(SSPS_FULL, gd, (b - p) & 31);
         if (b - p >= 32) { const int jb = T.idof(b); gbb = __ldg(P.G + (size_t)jb * V + jb); }
         double inv, wb;
         chol_pivot(d2, gbb, tb, inv, wb, q);
-        __syncwarp();                               // every lane has read d2 and t_b
-        if (lane == 0) { rb[SCOL(b)] = inv; tw[b + 1] = wb; }
-        for (int a = b + 1 + lane; a < kr; a += 32) { double* ra = SROW(a); ra[SCOL(b)] = ra[SCOL(b)] * inv; }
-        __syncwarp();                               // column b is final
-        for (int a = b + 1 + lane; a < kr; a += 32) {
-            double* ra = SROW(a);
-            const double lab = ra[SCOL(b)];
-            for (int c = b + 1; c < a; ++c) ra[SCOL(c)] = fma(-lab, SROW(c)[SCOL(b)], ra[SCOL(c)]);
-            ra[SCOL(a)] = fma(-lab, lab, ra[SCOL(a)]);
-            tw[a + 1] = fma(-lab, wb, tw[a + 1]);
+        // the next pivot's inputs first: the owner of row b + 1 needs one product
+        const int own = (b + 1 - p) & 31;
+        double d2n = 0.0, tn = 0.0;
+        if (b + 1 < kr && lane == own) {
+            const double* rn = SROW(b + 1);
+            const double l = rn[SCOL(b)] * inv;
+            d2n = fma(-l, l, rn[SCOL(b + 1)]);
+            tn = fma(-l, wb, tw[b + 2]);
         }
-        __syncwarp();
+        d2n = __shfl_sync(SSPS_FULL, d2n, own);
+        tn = __shfl_sync(SSPS_FULL, tn, own);
+        double lab_keep[SSPS_KU];
+#pragma unroll
+        for (int u = 0; u < SSPS_KU; ++u) {
+            lab_keep[u] = 0.0;
+            const int a = p + lane + 32 * u;
+            if (a > b && a < kr) {
+                double* ra = SROW(a);
+                const double lab = ra[SCOL(b)] * inv;
+                for (int c = b + 1; c < a; ++c) ra[SCOL(c)] = fma(-lab, SROW(c)[SCOL(b)] * inv, ra[SCOL(c)]);
+                ra[SCOL(a)] = fma(-lab, lab, ra[SCOL(a)]);
+                tw[a + 1] = fma(-lab, wb, tw[a + 1]);
+                lab_keep[u] = lab;
+            }
+        }
+        __syncwarp();                               // nobody reads the unscaled column b any more
+#pragma unroll
+        for (int u = 0; u < SSPS_KU; ++u) {
+            const int a = p + lane + 32 * u;
+            if (a > b && a < kr) SROW(a)[SCOL(b)] = lab_keep[u];
+        }
+        if (lane == 0) { SROW(b)[SCOL(b)] = inv; tw[b + 1] = wb; }
+        d2 = d2n; tb = tn;
     }
     __syncwarp();
+#ifdef SSPS_PROFILE_BIG
+    if (lane == 0) { atomicAdd(prof + 28, (unsigned long long)(tp1_ - tp0_)); atomicAdd(prof + 29, (unsigned long long)(clock64() - tp1_)); atomicAdd(prof + 30, (unsigned long long)nt); atomicAdd(prof + 31, 1ull); }
+#endif
 #undef SROW
 #undef SCOL
     return q;
@@ -1123,7 +1160,11 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
         const int pd = has_rem ? p : SSPS_NODEAD;
         if (has_rem) {
             ids_remove(T, k, p, lane);
+#ifdef SSPS_PROFILE_BIG
+            q_new = fac_remove(P, Ri, T, k, p, q_new, lane, C.stats);
+#else
             q_new = fac_remove(P, Ri, T, k, p, q_new, lane);
+#endif
             kr = k - 1;
         }
 

@@ -45,3 +45,6 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
         tot = float(r[16:24].sum()) or 1.0
         print("BIG phase cycles by section (profiling build): " + ", ".join("%s %.1f%%" % (n, 100 * r[16 + e] / tot) for e, n in enumerate(names)),
               "| per big lane-step %.0f" % (tot / max(st.n_big_steps, 1)))
+        if r[31]:
+            print("fac_remove: %d calls, mean trailing rows %.1f, partial sums %.0f cycles, trailing loop %.0f cycles per call (%.0f per pivot)"
+                  % (r[31], r[30] / r[31], r[28] / r[31], r[29] / r[31], r[29] / max(r[30], 1)))
