@@ -249,6 +249,17 @@ int  ssps_psrf_global(ssps_handle* const* handles, int32_t n, double burnin, dou
 int  ssps_edge_posterior_global(ssps_handle* const* handles, int32_t n, double burnin, double* probs_child_major,
                                 double* lambda_mean, int64_t* burnin_used, int64_t* n_used, int64_t* n_chains_total);
 
+/* K5: evaluate_convergence + evaluate_summary (scripts/postprocess_samples.jl:58-191) on the device, from the change-point
+ * logs of the chains of the given handles (all in this process; needs record_changepoints = 1): for every edge indicator
+ * and every lambda_i the pooled post-burn-in mean, the split-chain PSRF and N_eff (variogram sum with the reference's
+ * stopping rule) at stop point `length` (0 = all recorded samples).  Burn-in index floor(burnin * length) and split index
+ * are EXACT (no snapshot grid).  Edge outputs V*V child-major, lambda outputs V; any may be NULL.  PSRF is NaN where the
+ * within-chain variance is 0, as in the reference (JSON null). */
+int  ssps_convergence(ssps_handle* const* handles, int32_t n, double burnin, int64_t length,
+                      double* edge_mean, double* edge_psrf, double* edge_neff,
+                      double* lambda_mean, double* lambda_psrf, double* lambda_neff,
+                      int64_t* burnin_index, int64_t* split_index);
+
 int  ssps_get_stats(ssps_handle* h, ssps_run_stats* out);
 int  ssps_get_khist(ssps_handle* h, int64_t* hist, int32_t len);
 /* The MH kernel's raw counter block (csrc/ssps_mh.cuh, enum ST_*), for profiling builds. */

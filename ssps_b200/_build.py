@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.environ.get("SSPS_LIB") or os.path.join(_HERE, "libssps_b200.so")   # SSPS_LIB: experiment builds
 SOURCES = [os.path.join(CSRC, "ssps_capi.cu")]
-DEPS = SOURCES + [os.path.join(CSRC, "ssps_kernels.cuh"), os.path.join(CSRC, "ssps_mh.cuh"), os.path.join(CSRC, "ssps_poly.cuh"),
+DEPS = SOURCES + [os.path.join(CSRC, "ssps_kernels.cuh"), os.path.join(CSRC, "ssps_mh.cuh"), os.path.join(CSRC, "ssps_poly.cuh"), os.path.join(CSRC, "ssps_neff.cuh"),
                   os.path.join(os.path.dirname(_HERE), "include", "ssps.h")]
 
 NVCC_FLAGS = [

@@ -84,6 +84,7 @@ SIGNATURES = {
     "ssps_run_multi": (C.c_int, [C.POINTER(_hp), C.c_int32, C.c_int64, C.c_double, C.c_int32, _lp]),
     "ssps_psrf_global": (C.c_int, [C.POINTER(_hp), C.c_int32, C.c_double, _dp, _dp, _dp]),
     "ssps_edge_posterior_global": (C.c_int, [C.POINTER(_hp), C.c_int32, C.c_double, _dp, _dp, _lp, _lp, _lp]),
+    "ssps_convergence": (C.c_int, [C.POINTER(_hp), C.c_int32, C.c_double, C.c_int64, _dp, _dp, _dp, _dp, _dp, _dp, _lp, _lp]),
     "ssps_get_stats": (C.c_int, [_hp, C.POINTER(RunStats)]),
     "ssps_get_khist": (C.c_int, [_hp, _lp, C.c_int32]),
     "ssps_get_raw_stats": (C.c_int, [_hp, _lp, C.c_int32]),

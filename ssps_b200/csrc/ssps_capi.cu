@@ -14,6 +14,7 @@
 #include "ssps_kernels.cuh"
 #include "ssps_mh.cuh"
 #include "ssps_poly.cuh"
+#include "ssps_neff.cuh"
 
 #include <algorithm>
 #include <chrono>
@@ -1836,6 +1837,115 @@ int ssps_edge_posterior_global(ssps_handle* const* hs, int32_t n, double burnin,
     if (burnin_used) *burnin_used = b0;
     if (n_used) *n_used = n0;
     if (n_chains_total) *n_chains_total = (int64_t)llround(denom / (double)(n0 - b0));
+    return SSPS_OK;
+}
+
+}  // extern "C"
+
+// ================================================================================================
+// K5: convergence statistics from the change-point logs (csrc/ssps_neff.cuh)
+// ================================================================================================
+namespace {
+
+template <bool BINARY>
+int run_neff(ssps_handle* h0, int Q, int C, const std::vector<long long>& off, const std::vector<int>& pos, const std::vector<double>& val,
+             int b, int s, int len, double* mean_out, double* psrf_out, double* neff_out) {
+    DevBuf<long long> d_off;
+    DevBuf<int> d_pos;
+    DevBuf<double> d_val, d_mean, d_psrf, d_neff;
+    CKS(upload(h0, d_off, off.data(), off.size()));
+    CKS(upload(h0, d_pos, pos.data(), std::max<size_t>(pos.size(), 1)));
+    CKS(upload(h0, d_val, val.data(), std::max<size_t>(val.size(), 1)));
+    CK(d_mean.alloc(Q)); CK(d_psrf.alloc(Q)); CK(d_neff.alloc(Q));
+    NeffLog lg{d_off.p, d_pos.p, d_val.p, C};
+    neff_kernel<BINARY><<<div_up((size_t)Q * 32, 128), 128, 0, h0->stream>>>(lg, Q, b, s, len, d_mean.p, d_psrf.p, d_neff.p);
+    CKS(launch_ok(h0, "neff_kernel"));
+    if (mean_out) CKS(download(h0, mean_out, d_mean.p, (size_t)Q));
+    if (psrf_out) CKS(download(h0, psrf_out, d_psrf.p, (size_t)Q));
+    if (neff_out) CKS(download(h0, neff_out, d_neff.p, (size_t)Q));
+    CK(cudaStreamSynchronize(h0->stream));
+    return SSPS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ssps_convergence(ssps_handle* const* hs, int32_t n, double burnin, int64_t length, double* edge_mean, double* edge_psrf,
+                     double* edge_neff, double* lambda_mean, double* lambda_psrf, double* lambda_neff, int64_t* burnin_index,
+                     int64_t* split_index) {
+    CKS(check_handles(hs, n));
+    if (!(burnin >= 0.0 && burnin < 1.0)) return fail(SSPS_ERR_INVALID, "burnin must be in [0, 1)");
+    const int V = hs[0]->V;
+    int C = 0;
+    for (int e = 0; e < n; ++e) {
+        ssps_handle* h = hs[e];
+        if (!h->cfg.record_changepoints) return fail(SSPS_ERR_UNAVAILABLE, "ssps_convergence needs the change-point log (record_changepoints = 1)");
+        if (h->n_chains <= 0) return fail(SSPS_ERR_INVALID, "handle %d has no chains", e);
+        if (h->samples_recorded != hs[0]->samples_recorded) return fail(SSPS_ERR_INVALID, "handles 0 and %d recorded %lld and %lld samples", e, (long long)hs[0]->samples_recorded, (long long)h->samples_recorded);
+        CKS(bind(h));
+        if (h->cp_parent.empty()) CKS(changepoints_begin(h));
+        C += h->n_chains;
+    }
+    const int64_t len = length > 0 ? length : hs[0]->samples_recorded;
+    if (len > hs[0]->samples_recorded) return fail(SSPS_ERR_INVALID, "stop point %lld beyond the %lld recorded samples", (long long)len, (long long)hs[0]->samples_recorded);
+    const int64_t b = (int64_t)floor(burnin * (double)len);            // postprocess_samples.jl:167
+    const int64_t s = b + (len - b) / 2;                               // :168
+    if (s - b < 3 || len - s < 3) return fail(SSPS_ERR_UNAVAILABLE, "%lld samples are too few for split-chain statistics", (long long)len);
+    if (len > 2000000000LL) return fail(SSPS_ERR_UNSUPPORTED, "stop point beyond 2^31 samples");
+    if (burnin_index) *burnin_index = b;
+    if (split_index) *split_index = s;
+    CKS(bind(hs[0]));
+    // ---- edge indicators: Q = V * V sequences per chain ----
+    if (edge_mean || edge_psrf || edge_neff) {
+        const size_t Q = (size_t)V * V;
+        std::vector<long long> off(Q * C + 1, 0);
+        int c0 = 0;
+        for (int e = 0; e < n; ++e) {
+            for (int c = 0; c < hs[e]->n_chains; ++c)
+                for (const ParentEvent& ev : hs[e]->cp_parent[c]) ++off[((size_t)ev.child * V + ev.parent) * C + (c0 + c) + 1];
+            c0 += hs[e]->n_chains;
+        }
+        for (size_t i = 0; i < Q * C; ++i) off[i + 1] += off[i];
+        std::vector<int> pos((size_t)off[Q * C]);
+        std::vector<double> val((size_t)off[Q * C]);
+        std::vector<long long> fill(off.begin(), off.end() - 1);
+        c0 = 0;
+        for (int e = 0; e < n; ++e) {
+            for (int c = 0; c < hs[e]->n_chains; ++c)
+                for (const ParentEvent& ev : hs[e]->cp_parent[c]) {      // time order inside every (child, parent): kept by the stable fill
+                    const long long at = fill[((size_t)ev.child * V + ev.parent) * C + (c0 + c)]++;
+                    pos[(size_t)at] = (int)ev.n; val[(size_t)at] = (double)ev.value;
+                }
+            c0 += hs[e]->n_chains;
+        }
+        CKS(run_neff<true>(hs[0], (int)Q, C, off, pos, val, (int)b, (int)s, (int)len, edge_mean, edge_psrf, edge_neff));
+    }
+    // ---- lambda_i: Q = V real-valued sequences per chain ----
+    if (lambda_mean || lambda_psrf || lambda_neff) {
+        const size_t Q = (size_t)V;
+        std::vector<long long> off(Q * C + 1, 0);
+        int c0 = 0;
+        for (int e = 0; e < n; ++e) {
+            for (int c = 0; c < hs[e]->n_chains; ++c)
+                for (const LambdaEvent& ev : hs[e]->cp_lambda[c]) ++off[(size_t)ev.child * C + (c0 + c) + 1];
+            c0 += hs[e]->n_chains;
+        }
+        for (size_t i = 0; i < Q * C; ++i) off[i + 1] += off[i];
+        std::vector<int> pos((size_t)off[Q * C]);
+        std::vector<double> val((size_t)off[Q * C]);
+        std::vector<long long> fill(off.begin(), off.end() - 1);
+        c0 = 0;
+        for (int e = 0; e < n; ++e) {
+            for (int c = 0; c < hs[e]->n_chains; ++c)
+                for (const LambdaEvent& ev : hs[e]->cp_lambda[c]) {
+                    const long long at = fill[(size_t)ev.child * C + (c0 + c)]++;
+                    pos[(size_t)at] = (int)ev.n; val[(size_t)at] = ev.value;
+                }
+            c0 += hs[e]->n_chains;
+        }
+        CKS(run_neff<false>(hs[0], (int)Q, C, off, pos, val, (int)b, (int)s, (int)len, lambda_mean, lambda_psrf, lambda_neff));
+    }
     return SSPS_OK;
 }
 

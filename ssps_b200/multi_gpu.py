@@ -193,6 +193,21 @@ class MultiGpuSampler:
     def edge_posterior(self, burnin: float = 0.5):
         return _edge_posterior_global(self.samplers, burnin)
 
+    def convergence(self, burnin: float = 0.5, length: int = 0):
+        """Pooled over all GPUs' chains (the logs live on the host of this one process; computed on the first device)."""
+        return self.samplers[0].convergence(burnin, length, others=self.samplers[1:])
+
+    @property
+    def n_chains(self):
+        return self.n_chains_total
+
+    @property
+    def record_changepoints(self):
+        return bool(self.samplers[0].cfg.record_changepoints)
+
+    def samples_recorded(self) -> int:
+        return int(self.samplers[0].stats().samples_recorded)
+
     def locate(self, chain: int) -> Tuple[Sampler, int]:
         """(sampler, local index) of global chain id `chain`."""
         for s, (first, count) in zip(self.samplers, self.shards):

@@ -1,19 +1,24 @@
 """Pooled edge posterior / convergence summary in the format of the reference's
-scripts/postprocess_samples.jl (:212-233), produced directly from the device tallies so that
-scoring.jl / score_dream.py / json_to_genie.py consume many-chain runs without per-chain JSON.
+scripts/postprocess_samples.jl (:212-233), produced directly on the device so that scoring.jl / score_dream.py /
+json_to_genie.py consume many-chain runs without per-chain JSON files.  Exactly the reference's keys:
 
     {"parent_sets": V x V probabilities [child][parent], "edge_conf_key": "parent_sets",
-     "conv_stats": {"parent_sets": [[ [[psrf, n_eff]] per parent ] per child ], "lambda": [...]},
-     "summary": {"lambda": [...]}, "stop_points": [n], "t_elapsed": [...], "n": [...]}
+     "conv_stats": {"parent_sets": [[ [[psrf, n_eff] per stop point] per parent ] per child ], "lambda": [...]},
+     "summary": {"lambda": [...]}, "stop_points": [...], "t_elapsed": [...], "n": [...]}
 
-PSRF follows compute_psrf_neff (:99-138) incl. its 1/M between-chain variance (quirk Q6); NaN
-(constant indicator, W = 0) is written as null exactly like JSON.print does.  N_eff needs lagged
-autocorrelations of the dense sequences (:58-94), which the tallies do not hold: it is written as
-null here and is available per chain from the change-point JSON through the reference's own script.
+Two sources:
+  * the change-point log (record_changepoints = 1): ssps_convergence (K5, csrc/ssps_neff.cuh) evaluates compute_psrf_neff
+    (:99-138) and correlation_sum (:58-91) per edge and per lambda_i at the reference's EXACT burn-in / split indices,
+    N_eff included -- what tests/test_gpu_summary.py compares with this module's host twin of the reference's script;
+  * the tallies only (thousands of chains, no log): PSRF from the snapshot-aligned tallies (K4), N_eff = null, and the
+    indices actually used are reported under the extension key "ssps_b200" (a consumer of the reference's format ignores it).
+PSRF follows the reference incl. its 1/M between-chain variance (quirk Q6); NaN (constant indicator, W = 0) is written
+as null exactly like JSON.print does.
 """
 from __future__ import annotations
 
 import math
+import warnings
 
 
 def _num(x):
@@ -21,25 +26,56 @@ def _num(x):
     return x if math.isfinite(x) else None
 
 
-def summarize_sampler(sampler, burnin: float = 0.5, t_elapsed: float = 0.0) -> dict:
-    V = sampler.V
-    probs, lam_mean, b_used, n_used = sampler.edge_posterior(burnin)
-    try:
-        mx, edge_psrf, lam_psrf = sampler.psrf_finish(sampler.psrf_sums(burnin))
-    except Exception:            # not enough snapshots yet: PSRF undefined
-        mx, edge_psrf, lam_psrf = float("nan"), None, None
-    conv_ps = [[[[_num(edge_psrf[i][j]) if edge_psrf is not None else None, None]] for j in range(V)] for i in range(V)]
-    conv_lam = [[[_num(lam_psrf[i]) if lam_psrf is not None else None, None]] for i in range(V)]
+def _has_log(sampler) -> bool:
+    if hasattr(sampler, "record_changepoints"):
+        return bool(sampler.record_changepoints)
+    return bool(sampler.cfg.record_changepoints)
+
+
+def _n_recorded(sampler) -> int:
+    return int(sampler.samples_recorded()) if hasattr(sampler, "samples_recorded") else int(sampler.stats().samples_recorded)
+
+
+def summarize_sampler(sampler, burnin: float = 0.5, t_elapsed: float = 0.0, stop_points=()) -> dict:
+    """collect_stats (:212-233) for the chains of a Sampler / MultiGpuSampler, computed on the device."""
+    from ._lib import ERR_UNAVAILABLE, SspsError
+    V, n = sampler.V, _n_recorded(sampler)
+    stops = [int(sp) for sp in stop_points if sp <= n] if len(stop_points) else [n]
+    if _has_log(sampler):
+        full = sampler.convergence(burnin, n)                    # evaluate_summary ignores the stop points (:183-191)
+        per_stop = [full if sp == n else sampler.convergence(burnin, sp) for sp in stops]
+        conv_ps = [[[[_num(c["edge_psrf"][i][j]), _num(c["edge_neff"][i][j])] for c in per_stop] for j in range(V)] for i in range(V)]
+        conv_lam = [[[_num(c["lambda_psrf"][i]), _num(c["lambda_neff"][i])] for c in per_stop] for i in range(V)]
+        probs, lam_mean = full["edge_mean"], full["lambda_mean"]
+        ext = {"source": "change-point log (K5)", "burnin_index": [int(c["burnin_index"]) for c in per_stop],
+               "split_index": [int(c["split_index"]) for c in per_stop]}
+    else:
+        out = sampler.edge_posterior(burnin)
+        probs, lam_mean, b_used, n_used = out[0], out[1], out[2], out[3]
+        want = int(math.floor(burnin * n_used))
+        if b_used != want:
+            warnings.warn("edge posterior: burn-in index %d instead of floor(%g * %d) = %d (tally snapshots lie on a grid; "
+                          "lower psrf_grid or keep the change-point log for the exact index)" % (b_used, burnin, n_used, want))
+        try:
+            res = sampler.psrf(burnin) if not hasattr(sampler, "psrf_sums") else sampler.psrf_finish(sampler.psrf_sums(burnin))
+            mx, edge_psrf, lam_psrf = res[0], res[1], (res[2] if len(res) > 2 else None)
+        except SspsError as e:       # not enough snapshots yet: PSRF undefined.  Anything else (CUDA, memory) is an error
+            if e.code != ERR_UNAVAILABLE:
+                raise
+            mx, edge_psrf, lam_psrf = float("nan"), None, None
+        stops = [int(n_used)]
+        conv_ps = [[[[_num(edge_psrf[i][j]) if edge_psrf is not None else None, None]] for j in range(V)] for i in range(V)]
+        conv_lam = [[[_num(lam_psrf[i]) if lam_psrf is not None else None, None]] for i in range(V)]
+        ext = {"source": "tallies (K4): N_eff needs the change-point log", "burnin_index": [int(b_used)], "max_edge_psrf": _num(mx)}
     return {
+        "stop_points": stops,
+        "summary": {"lambda": [float(x) for x in lam_mean]},
+        "conv_stats": {"parent_sets": conv_ps, "lambda": conv_lam},
         "parent_sets": [[float(probs[i][j]) for j in range(V)] for i in range(V)],
         "edge_conf_key": "parent_sets",
-        "conv_stats": {"parent_sets": conv_ps, "lambda": conv_lam},
-        "summary": {"lambda": [float(x) for x in lam_mean]},
-        "stop_points": [int(n_used)],
-        "burnin_index": int(b_used),
-        "max_edge_psrf": _num(mx),
         "t_elapsed": [float(t_elapsed)] * sampler.n_chains,
-        "n": [int(n_used)] * sampler.n_chains,
+        "n": [int(n)] * sampler.n_chains,
+        "ssps_b200": ext,
     }
 
 

@@ -265,6 +265,23 @@ class Sampler:
         check(self._L.ssps_psrf(self._h, float(burnin), C.byref(mx), _d(edge)))
         return mx.value, edge
 
+    def convergence(self, burnin: float = 0.5, length: int = 0, others: Sequence["Sampler"] = ()):
+        """ssps_convergence: evaluate_convergence + evaluate_summary of postprocess_samples.jl on the device, from the
+        change-point logs of this sampler's chains (and those of `others`, pooled).  Returns a dict with V x V arrays
+        edge_mean / edge_psrf / edge_neff, length-V arrays lambda_mean / lambda_psrf / lambda_neff, and the exact
+        burn-in and split indices."""
+        hs = [self] + list(others)
+        arr = (C.c_void_p * len(hs))(*[x._h for x in hs])
+        V = self.V
+        out = {k: np.zeros((V, V)) for k in ("edge_mean", "edge_psrf", "edge_neff")}
+        out.update({k: np.zeros(V) for k in ("lambda_mean", "lambda_psrf", "lambda_neff")})
+        b, sp = C.c_int64(0), C.c_int64(0)
+        check(self._L.ssps_convergence(arr, len(hs), float(burnin), int(length), _d(out["edge_mean"]), _d(out["edge_psrf"]),
+                                       _d(out["edge_neff"]), _d(out["lambda_mean"]), _d(out["lambda_psrf"]), _d(out["lambda_neff"]),
+                                       C.byref(b), C.byref(sp)))
+        out["burnin_index"], out["split_index"] = b.value, sp.value
+        return out
+
     # ------------------------------------------------------------------ change points
     def changepoints(self, chain: int):
         npar, nlam = C.c_int64(0), C.c_int64(0)

@@ -44,7 +44,9 @@ def main():
         raw_timestep=ts["timestep"].to_numpy(dtype=np.float64),
         var_names=np.array(var_names), node_names=np.array(names),
         series_lengths=np.array([s.shape[0] for s in series]),
-        Xminus=xm, Xplus=xp, prior=prior, genie_scores=scores)
+        Xminus=xm, Xplus=xp, prior=prior, genie_scores=scores,
+        # the key columns of the reference's baseline file, in file order: what tests/ssps_csv.sh diffs (csvdiff on node1,node2)
+        genie_node1=np.array([str(x) for x in genie["node1"]]), genie_node2=np.array([str(x) for x in genie["node2"]]))
     print("wrote", OUT, "V=%d n=%d series=%s" % (V, xm.shape[0], [s.shape[0] for s in series]))
 
 
