@@ -91,12 +91,13 @@ def run_reference(args, rank, world):
         return
     from oracle import oracle as orc
     ds, xm, xp = make_workload(args.V, args.T, args.M)
-    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std)
+    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, regression_deg=args.deg)
     cores = os.cpu_count() or 1
     chains = cores
     # size one step for ~3 s of CPU work
-    t, nprop, _ = P.run_chains_mt(chains, cores, 2000, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
-    sweeps = max(2000, int(2000 * 3.0 / max(t, 1e-3)))
+    probe = args.cpu_probe_sweeps
+    t, nprop, _ = P.run_chains_mt(chains, cores, probe, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    sweeps = max(probe, int(probe * 3.0 / max(t, 1e-3)))
     for w in range(args.warmup):
         P.run_chains_mt(chains, cores, sweeps, seed=2 + w, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
     tot_t, tot_p = 0.0, 0
@@ -108,10 +109,10 @@ def run_reference(args, rank, world):
     value = tot_p / tot_t
     sample = "%d chains x %d sweeps per step on %d threads (oracle QR scorer + [i;S] lml cache)" % (chains, sweeps, cores)
     emit_line(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "impl": "reference", "metric": args.metric, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "simulate_data.jl restatement V=%d T=%d M=%d (n=%d), deg 1" % (args.V, args.T, args.M, P.n),
+        "config": {"workload": "%s: simulate_data.jl restatement V=%d T=%d M=%d (n=%d), regression_deg %s" % (args.workload, args.V, args.T, args.M, P.n, args.deg_label),
                    "chains": chains, "sweeps_per_step": sweeps},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -120,10 +121,10 @@ def run_reference(args, rank, world):
     }))
 
 
-def _cpu_rate_sample(P, orc, cores, target_s):
+def _cpu_rate_sample(P, orc, cores, target_s, probe=2000):
     """Run the reference-faithful oracle on all cores for about target_s seconds; returns (seconds, proposals, sweeps)."""
-    t, nprop, _ = P.run_chains_mt(cores, cores, 2000, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
-    sweeps = max(2000, int(2000 * target_s / max(t, 1e-3)))
+    t, nprop, _ = P.run_chains_mt(cores, cores, probe, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
+    sweeps = max(probe, int(probe * target_s / max(t, 1e-3)))
     t, nprop, _ = P.run_chains_mt(cores, cores, sweeps, seed=3, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
     return t, nprop, sweeps
 
@@ -131,9 +132,9 @@ def _cpu_rate_sample(P, orc, cores, target_s):
 def cpu_baseline(args):
     from oracle import oracle as orc
     ds, xm, xp = make_workload(args.V, args.T, args.M)
-    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std)
+    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, regression_deg=args.deg)
     cores = os.cpu_count() or 1
-    t, nprop, sweeps = _cpu_rate_sample(P, orc, cores, 20.0)
+    t, nprop, sweeps = _cpu_rate_sample(P, orc, cores, 20.0, probe=args.cpu_probe_sweeps)
     return {"value": nprop / t, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": "%d chains x %d sweeps (%.1f s) of the same workload, oracle QR scorer + [i;S] lml cache, one chain per thread"
                       % (cores, sweeps, t)}
@@ -163,7 +164,7 @@ def time_to_psrf_cpu(args):
     from concurrent.futures import ThreadPoolExecutor
     from oracle import oracle as orc
     ds, xm, xp = make_workload(args.V, args.T, args.M)
-    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std)
+    P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, regression_deg=args.deg)
     cores = os.cpu_count() or 1
     chains = []
     for c in range(cores):
@@ -203,7 +204,7 @@ def time_to_psrf_gpu(args, rank, world, local_rank, stream, dev, chains_per_gpu=
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    smp = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=args.psrf_check // 4)
+    smp = Sampler(device=local_rank, regression_deg=args.deg, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=args.psrf_check // 4)
     smp.set_stream(stream.cuda_stream)
     smp.set_data(xm, xp, ds.prior_graph)
     smp.generate(C, seed=args.seed + 17, chain_id_offset=rank * C)
@@ -253,11 +254,12 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    smp = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=max(S // 4, 1))
+    smp = Sampler(device=local_rank, regression_deg=args.deg, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=max(S // 4, 1))
     smp.set_stream(stream.cuda_stream)
     smp.set_data(xm, xp, ds.prior_graph)
     smp.generate(C, seed=args.seed, chain_id_offset=rank * C)
     fp64_peak = smp.measure_fp64_peak()
+    gather_peaks = smp.measure_gather_peak(2 * V * V * 8)          # G + R
     sums = torch.zeros(smp.psrf_sums_len(), dtype=torch.float64, device=dev)
 
     def step():
@@ -321,21 +323,36 @@ def run_ours(args, rank, world, local_rank):
     tier_mix = {"small": 1.0 - (big_steps + mid_steps) / max(nprop_local, 1), "mid": mid_steps / max(nprop_local, 1),
                 "big": big_steps / max(nprop_local, 1),
                 "what": "share of the timed proposals scored in each storage tier (|S| <= 5 registers+smem, 6..15 lane-owned Stage, >= 16 warp-cooperative)"}
+    is_poly = args.deg >= 2
+    gather = gbytes / (k_ms * 1e-3) / 1e9
     roofline = {"bound": "fp64", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": traffic,
-                "kernel": "mh_sweeps_kernel<PhiloxSource>", "launches": launches, "avg_launch_ms": k_ms / max(launches, 1),
+                "kernel": "mh_poly_kernel<PhiloxSource>" if is_poly else "mh_sweeps_kernel<PhiloxSource>", "launches": launches,
+                "avg_launch_ms": k_ms / max(launches, 1),
                 "kernel_share_of_step": k_ms / ms,
                 "peak_source": "DFMA peak measured on this GPU by ssps_measure_fp64_peak (MEASURED_PEAKS.json has no FP64 figure)",
                 "mean_k": (st1.sum_k - st0.sum_k) / max(nprop_local, 1),
                 "algorithmic_flops_per_proposal": flops / max(nprop_local, 1),
-                "gather_GBps": gbytes / (k_ms * 1e-3) / 1e9,
-                "kernel_proposals_per_s": nprop_local / (k_ms * 1e-3),
-                "note": "the FP64 fraction is small by construction (33 flops per proposal); the kernel is bound by issue latency "
-                        "(L1/L2 gathers, dependent fp64 chains, the lock-step barrier; instruction fetch before the lock-step): see "
-                        "issue_slot_utilisation_pct and stall_cycles_per_issue (ncu, profiles/)",
-                "hbm": hbm_view(traffic, k_ms / max(launches, 1)),
-                "ncu": None if ncu is None else {k: ncu[k] for k in ("source", "launch", "issue_slot_utilisation_pct", "fp64_pipe_active_pct",
-                                                                    "warp_instructions_per_launch", "stall_cycles_per_issue",
-                                                                    "l1_hit_pct", "l2_hit_pct", "registers_per_thread")}}
+                "kernel_proposals_per_s": nprop_local / (k_ms * 1e-3)}
+    if is_poly:
+        roofline["note"] = ("interaction columns (regression_deg %s): every proposal scored from scratch, F = n m (m + 5) + m^3/3 + 2 m^2 + 2 m flops for a "
+                            "design of m columns (SURVEY 8d, deg > 1; saturated designs are closed form and count 0); see DESIGN.md for the tiers" % args.deg_label)
+    else:
+        roofline.update({
+            "gather_GBps": gather,
+            "gather": {"achieved": gather, "unit": "GB/s (useful bytes: 8 per gathered double of G / R, SURVEY 8d B(k))",
+                       "l1_peak": gather_peaks[0], "l2_peak": gather_peaks[1], "smem_peak": gather_peaks[2],
+                       "frac_l1": gather / gather_peaks[0] if gather_peaks[0] else None,
+                       "frac_l2": gather / gather_peaks[1] if gather_peaks[1] else None,
+                       "frac_smem": gather / gather_peaks[2] if gather_peaks[2] else None,
+                       "peak_source": "ssps_measure_gather_peak on this GPU: random 8-byte loads from a %d kB table (= G + R), 8 in flight per thread, all SMs; "
+                                      "l1 = the kernel's ld.global.nc path, l2 = ld.global.cg, smem = shared memory" % (2 * V * V * 8 // 1000)},
+            "note": "the FP64 fraction is small by construction (33 flops per proposal); the kernel is bound by issue latency "
+                    "(L1/L2 gathers, dependent fp64 chains, the lock-step barrier; instruction fetch before the lock-step): see "
+                    "issue_slot_utilisation_pct and stall_cycles_per_issue (ncu, profiles/)",
+            "hbm": hbm_view(traffic, k_ms / max(launches, 1)),
+            "ncu": None if ncu is None else {k: ncu[k] for k in ("source", "launch", "issue_slot_utilisation_pct", "fp64_pipe_active_pct",
+                                                                "warp_instructions_per_launch", "stall_cycles_per_issue",
+                                                                "l1_hit_pct", "l2_hit_pct", "registers_per_thread")}})
 
     # ---- e2e: host buffers in, posterior out, every step ----
     e2e = None
@@ -348,7 +365,7 @@ def run_ours(args, rank, world, local_rank):
 
         def e2e_step(seed):
             tp = [time.perf_counter()]
-            s2 = Sampler(device=local_rank, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=S // 4)
+            s2 = Sampler(device=local_rank, regression_deg=args.deg, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, psrf_grid=S // 4)
             s2.set_stream(stream.cuda_stream)
             tp.append(time.perf_counter())
             s2.set_data(xm_h, xp_h, pr_h)
@@ -405,12 +422,13 @@ def run_ours(args, rank, world, local_rank):
     if rank != 0:
         return
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "metric": args.metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "simulate_data.jl restatement V=%d T=%d M=%d (n=%d), regression_deg 1, lambda_prop_std %g, large_indeg %g, thinning 1"
-                               % (V, args.T, args.M, smp.n, args.lambda_prop_std, args.large_indeg),
-                   "chains_per_gpu": C, "sweeps_per_step": S, "parallelism": "chains sharded over %d GPU(s), no data-path collective; one PSRF all-reduce per timed region" % world,
+        "config": {"workload": "%s: simulate_data.jl restatement V=%d T=%d M=%d (n=%d), regression_deg %s, lambda_prop_std %g, large_indeg %g, thinning 1"
+                               % (args.workload, V, args.T, args.M, smp.n, args.deg_label, args.lambda_prop_std, args.large_indeg),
+                   "chains_per_gpu": C, "chains_total": C * world, "sweeps_per_step": S,
+                   "parallelism": "chains sharded over %d GPU(s), no data-path collective; one PSRF all-reduce per timed region" % world,
                    "l2": "chain state + tallies (%.0f MB) exceed L2; G/R tables (%.0f kB) are cache-resident by design" % (2 * C * V * V * 4 / 1e6, 2 * V * V * 8 / 1e3)},
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(st1.kernel_launches - st0.kernel_launches),
         "sweeps_before_timed_region": int(st0.sweeps_done), "tier_mix": tier_mix,
@@ -469,11 +487,18 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
-    ap.add_argument("--V", type=int, default=100)
-    ap.add_argument("--T", type=int, default=8)
+    ap.add_argument("--workload", default="metric", choices=("metric", "c4", "c5"),
+                    help="metric: BASELINE.json's metric point (V=100, n=28, 4096 chains per GPU, weak scaling); "
+                         "c4: V=200, T=100, 1024 chains IN TOTAL sharded over the GPUs (strong scaling); "
+                         "c5: V=1000, T=100, regression_deg full, 512 chains per GPU (4096 on 8)")
+    ap.add_argument("--scaling", default=None, choices=("weak", "strong"), help="strong: --chains is the TOTAL, split over the GPUs")
+    ap.add_argument("--V", type=int, default=None)
+    ap.add_argument("--T", type=int, default=None)
     ap.add_argument("--M", type=int, default=4)
-    ap.add_argument("--chains", type=int, default=4096, help="chains per GPU")
-    ap.add_argument("--sweeps", type=int, default=400, help="sweeps per step")
+    ap.add_argument("--deg", default=None, help="regression_deg: an integer, or 'full' (= 64 >= |S|: all non-empty product subsets, quirk Q2)")
+    ap.add_argument("--chains", type=int, default=None, help="chains per GPU (weak scaling) or in total (strong scaling)")
+    ap.add_argument("--sweeps", type=int, default=None, help="sweeps per step")
+    ap.add_argument("--cpu-probe-sweeps", type=int, default=None, help="first probe of the CPU arm (sized down for the slow interaction designs)")
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--large-indeg", type=float, default=15.0)
     ap.add_argument("--lambda-prop-std", type=float, default=3.0)
@@ -489,6 +514,28 @@ def main():
     args = ap.parse_args()
     if args.psrf_max_seconds is None:
         args.psrf_max_seconds = 240.0 if args.impl == "reference" else 90.0
+    preset = {"metric": dict(V=100, T=8, deg="1", chains=4096, sweeps=400, scaling="weak", probe=2000),
+              "c4": dict(V=200, T=100, deg="1", chains=1024, sweeps=400, scaling="strong", probe=200),
+              "c5": dict(V=1000, T=100, deg="full", chains=512, sweeps=8, scaling="weak", probe=1)}[args.workload]
+    args.V = args.V or preset["V"]; args.T = args.T or preset["T"]
+    args.deg_label = args.deg or preset["deg"]
+    args.deg = 64 if args.deg_label == "full" else int(args.deg_label)
+    args.scaling = args.scaling or preset["scaling"]
+    args.chains = args.chains or preset["chains"]
+    args.sweeps = args.sweeps or preset["sweeps"]
+    args.cpu_probe_sweeps = args.cpu_probe_sweeps or preset["probe"]
+    args.metric = METRIC if args.V == 100 else METRIC.replace("V=100", "V=%d" % args.V)
+    if args.workload != "metric":
+        args.no_psrf = True         # M2 is quoted on the metric point only
+    if args.workload == "c5" and args.impl != "reference":
+        # the reference's algorithm (and its restatement) builds B explicitly: a model-drawn start of C5 has sets of up to ~20 parents,
+        # i.e. 396 x 2^20 designs -- neither Julia nor the oracle can score them; no CPU figure exists for this workload
+        args.no_cpu_baseline = True
+    world_ = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.scaling == "strong":    # fixed total work: the chains are split over the ranks
+        if args.chains % world_:
+            ap.error("--scaling strong: %d chains do not split over %d GPUs" % (args.chains, world_))
+        args.chains //= world_
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

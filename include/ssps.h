@@ -270,6 +270,11 @@ int  ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles /* V */, int32_t* mean
 /* Device-side microbenchmark used by bench.py for the FP64 roofline denominator: dependent-free
  * DFMA streams on every SM; returns achieved TFLOP/s. */
 int  ssps_measure_fp64_peak(ssps_handle* h, double* tflops);
+/* The same for the gather roofline (achieved_gather / measured L2 or shared-memory bandwidth): random 8-byte
+ * loads from a table of `table_bytes` (pass the size of G + R), 8 in flight per thread, all SMs.  Returns USEFUL GB/s
+ * (8 bytes per load) through the read-only L1 path the kernel uses (l1_gbs), from L2 only (ld.global.cg, l2_gbs) and from
+ * shared memory (smem_gbs); any pointer may be NULL. */
+int  ssps_measure_gather_peak(ssps_handle* h, int64_t table_bytes, double* l1_gbs, double* l2_gbs, double* smem_gbs);
 /* Device blocks released by destroyed handles are kept in a process-wide cache for the next handle of the same
  * shapes (cudaMalloc of the 100 MB-class buffers costs 2..100 ms).  This returns the cached blocks of `device` to the
  * driver; live handles are not affected.  No counterpart in the reference (Julia's GC owns its memory). */

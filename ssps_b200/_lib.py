@@ -90,6 +90,7 @@ SIGNATURES = {
     "ssps_get_raw_stats": (C.c_int, [_hp, _lp, C.c_int32]),
     "ssps_get_vertex_cost": (C.c_int, [_hp, _lp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "ssps_measure_fp64_peak": (C.c_int, [_hp, _dp]),
+    "ssps_measure_gather_peak": (C.c_int, [_hp, C.c_int64, _dp, _dp, _dp]),
     "ssps_release_cached_memory": (C.c_int, [C.c_int32]),
 }
 

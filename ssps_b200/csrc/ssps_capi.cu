@@ -206,7 +206,8 @@ struct ssps_handle {
     SspsDev dev{};
     PolyDev poly{};                 // regression_deg != 1: interaction-column path (csrc/ssps_poly.cuh)
     bool is_poly = false;
-    DevBuf<double> poly_arena;
+    DevBuf<double> poly_arena, poly_warena;
+    int poly_mcap_p = 0;            // WARP tier column capacity (0: tier not needed)
     int poly_grid = 0;
 
     // ---- chains (K3) ----
@@ -569,19 +570,32 @@ int ssps_score(ssps_handle* h, int32_t n_sets, const int32_t* child, const int32
     const int block = 128, grid = div_up((size_t)n_sets, block);
     const size_t nthreads = (size_t)grid * block;
     if (h->is_poly) {       // interaction columns: every set from scratch (csrc/ssps_poly.cuh)
-        if (h->cfg.regression_deg > 0 && (kmax > SSPS_POLY_KMAX || poly_width(kmax, h->cfg.regression_deg) < 0))
-            return fail(SSPS_ERR_UNSUPPORTED, "regression_deg=%d: a set of %d parents needs more than %d design columns (or %d parents)",
-                        h->cfg.regression_deg, kmax, SSPS_POLY_MMAX, SSPS_POLY_KMAX);
+        int m_warp = 0;                                 // widest design the WARP tier will see
+        for (int s = 0; s < n_sets; ++s) {
+            const int k = set_offsets[s + 1] - set_offsets[s];
+            int m = 0;
+            const int cls = poly_class(k, h->cfg.regression_deg, h->n, m);
+            if (cls == PC_REFUSE || (cls != PC_SAT && cls != PC_EMPTY && k > SSPS_POLY_KLIST))
+                return fail(SSPS_ERR_UNSUPPORTED, "regression_deg=%d: set %d has %d parents and a design of fewer than n - 1 = %d columns; "
+                            "the interaction-column scorer handles at most %d parents for such sets", h->cfg.regression_deg, s, k, h->n - 1, SSPS_POLY_KW);
+            if (cls == PC_WARP) m_warp = std::max(m_warp, m);
+        }
+        const int mcap_p = (m_warp + 31) & ~31;
+        const size_t wdoubles = poly_warp_scratch_doubles(h->n, mcap_p);
+        int pgrid = std::min(grid, 4 * h->sm_count);
+        if (mcap_p) pgrid = std::max(1, std::min(pgrid, (int)((size_t)2 << 30) / (int)std::min<size_t>(4 * wdoubles * 8, (size_t)1 << 30)));   // <= 2 GB of WARP-tier scratch
+        const size_t pthreads = (size_t)pgrid * block;
         DevBuf<int> d_child, d_off, d_mem;
-        DevBuf<double> d_lam, d_lml, d_lp, arena;
+        DevBuf<double> d_lam, d_lml, d_lp, arena, warena;
         CKS(upload(h, d_child, child, (size_t)n_sets));
         CKS(upload(h, d_off, set_offsets, (size_t)n_sets + 1));
-        CKS(upload(h, d_mem, set_members, (size_t)total));
+        CKS(upload(h, d_mem, set_members, (size_t)std::max(total, 1)));
         if (lambda) CKS(upload(h, d_lam, lambda, (size_t)n_sets));
         CK(d_lml.alloc(n_sets)); CK(d_lp.alloc(n_sets));
-        CK(arena.alloc(nthreads * (size_t)SSPS_POLY_SCRATCH_DOUBLES));
-        poly_score_kernel<<<grid, block, 0, h->stream>>>(h->dev, h->poly, n_sets, d_child.p, d_off.p, d_mem.p, lambda ? d_lam.p : nullptr,
-                                                         arena.p, d_lml.p, logprior_out ? d_lp.p : nullptr);
+        CK(arena.alloc(pthreads * (size_t)SSPS_POLY_SCRATCH_DOUBLES));
+        CK(warena.alloc(pthreads / 32 * wdoubles));
+        poly_score_kernel<<<pgrid, block, 0, h->stream>>>(h->dev, h->poly, n_sets, d_child.p, d_off.p, d_mem.p, lambda ? d_lam.p : nullptr,
+                                                          arena.p, warena.p, mcap_p, d_lml.p, logprior_out ? d_lp.p : nullptr);
         CKS(launch_ok(h, "poly_score_kernel"));
         if (lml_out) CKS(download(h, lml_out, d_lml.p, (size_t)n_sets));
         if (logprior_out) CKS(download(h, logprior_out, d_lp.p, (size_t)n_sets));
@@ -657,27 +671,38 @@ int alloc_chains(ssps_handle* h, int n_chains) {
 
     // persistent MH grid: as many CTAs as stay resident, never more than there are warp-tasks
     h->mh_smem = SSPS_SMEM_BYTES;
-    int occ = 1 << 30;
+    int occ = 1;
     {
         // Shared memory holds only the SMALL-tier factors; what the carve-out leaves is L1 for the G / R / move
         // tables.  First find the register-limited occupancy with the largest carve-out, then shrink the
         // carve-out to what that many CTAs need (SSPS_CARVEOUT=<percent> overrides, for experiments).
-        const void* fns[4] = {(const void*)mh_sweeps_kernel<PhiloxSource, false>, (const void*)mh_sweeps_kernel<PhiloxSource, true>,
-                              (const void*)mh_sweeps_kernel<ReplaySource, false>, (const void*)mh_sweeps_kernel<ReplaySource, true>};
-        cudaDeviceProp prop;
-        CK(cudaGetDeviceProperties(&prop, h->device));
-        for (const void* f : fns) {
-            int o = 0;
-            CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-            CK(cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->mh_smem));
-            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, f, SSPS_BLOCK, h->mh_smem));
-            occ = std::min(occ, o);
+        // Once per device and process: cudaGetDeviceProperties and the attribute calls cost milliseconds (up to 100 ms
+        // measured on a fresh context), which a host that creates a handle per data set would pay on every one.
+        static std::mutex cfg_mu;
+        static std::map<int, int> cfg_occ;
+        std::lock_guard<std::mutex> g(cfg_mu);
+        auto it = cfg_occ.find(h->device);
+        if (it == cfg_occ.end()) {
+            int o_min = 1 << 30;
+            const void* fns[4] = {(const void*)mh_sweeps_kernel<PhiloxSource, false>, (const void*)mh_sweeps_kernel<PhiloxSource, true>,
+                                  (const void*)mh_sweeps_kernel<ReplaySource, false>, (const void*)mh_sweeps_kernel<ReplaySource, true>};
+            int smem_per_sm = 0;
+            CK(cudaDeviceGetAttribute(&smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, h->device));
+            for (const void* f : fns) {
+                int o = 0;
+                CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+                CK(cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->mh_smem));
+                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, f, SSPS_BLOCK, h->mh_smem));
+                o_min = std::min(o_min, o);
+            }
+            o_min = std::max(1, o_min);
+            int pct = (int)std::ceil(100.0 * (double)o_min * (double)(h->mh_smem + 1024) / (double)smem_per_sm) + 2;
+            if (const char* e = getenv("SSPS_CARVEOUT")) pct = atoi(e);
+            pct = std::max(0, std::min(100, pct));
+            for (const void* f : fns) CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+            it = cfg_occ.emplace(h->device, o_min).first;
         }
-        occ = std::max(1, occ);
-        int pct = (int)std::ceil(100.0 * (double)occ * (double)(h->mh_smem + 1024) / (double)prop.sharedMemPerMultiprocessor) + 2;
-        if (const char* e = getenv("SSPS_CARVEOUT")) pct = atoi(e);
-        pct = std::max(0, std::min(100, pct));
-        for (const void* f : fns) CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        occ = it->second;
     }
     occ = std::max(1, occ);
     if (const char* e = getenv("SSPS_MAX_OCC")) occ = std::max(1, std::min(occ, atoi(e)));      // experiments: resident CTAs per SM
@@ -711,8 +736,20 @@ int alloc_chains(ssps_handle* h, int n_chains) {
         int occ_p = 1;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_p, (const void*)mh_poly_kernel<PhiloxSource>, 128, 0));
         h->poly_grid = std::max(1, std::min(h->sm_count * std::max(1, occ_p), div_up((size_t)n_tasks, 4)));
+        // WARP tier: scratch for the widest design a set within max_indegree can have below saturation (csrc/ssps_poly.cuh);
+        // the grid shrinks if that scratch would take more than a quarter of the free memory
+        const int m_scored = poly_max_scored_width(std::min(h->kcap, SSPS_POLY_KLIST), h->cfg.regression_deg, h->n);
+        h->poly_mcap_p = m_scored > SSPS_POLY_MMAX ? ((m_scored + 31) & ~31) : 0;
+        const size_t wdoubles = poly_warp_scratch_doubles(h->n, h->poly_mcap_p);
+        if (h->poly_mcap_p) {
+            size_t free_b = 0, total_b = 0;
+            CK(cudaMemGetInfo(&free_b, &total_b));
+            const size_t per_cta = 4 * wdoubles * sizeof(double);
+            h->poly_grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)h->poly_grid, (free_b / 4) / per_cta));
+        }
         CK(h->poly_arena.alloc((size_t)h->poly_grid * 128 * SSPS_POLY_SCRATCH_DOUBLES));
-        h->kcap = std::min(h->kcap, SSPS_POLY_KMAX);
+        CK(h->poly_warena.alloc((size_t)h->poly_grid * 4 * wdoubles));
+        h->kcap = std::min(h->kcap, SSPS_POLY_KLIST);
     }
 
     h->thinning = 0; h->sweeps_done = 0; h->samples_recorded = 0;
@@ -983,10 +1020,10 @@ int run_launch(ssps_handle* h, RunCtx& cx) {
     if (h->is_poly) {
         if (cx.replay) {
             ReplaySource src{rp, C, V};
-            mh_poly_kernel<ReplaySource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p);
+            mh_poly_kernel<ReplaySource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p, h->poly_warena.p, h->poly_mcap_p);
         } else {
             PhiloxSource src{h->seed, h->chain_offset};
-            mh_poly_kernel<PhiloxSource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p);
+            mh_poly_kernel<PhiloxSource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p, h->poly_warena.p, h->poly_mcap_p);
         }
     } else if (cx.replay) {
         ReplaySource src{rp, C, V};
@@ -1057,7 +1094,13 @@ int ssps_init_chains(ssps_handle* h, int32_t n_chains, uint64_t seed, uint32_t c
     const bool explicit_state = init_offsets || init_members || init_lambda;
     if (explicit_state && (!init_offsets || !init_lambda))
         return fail(SSPS_ERR_INVALID, "init_offsets / init_members / init_lambda are all-or-nothing");
+    const bool trace = getenv("SSPS_TRACE") != nullptr;
+    const auto t_in = std::chrono::steady_clock::now();
+    const long long allocs_in = g_device_allocs;
     CKS(alloc_chains(h, n_chains));
+    if (trace)
+        fprintf(stderr, "[ssps trace] init_chains: buffers %.2f ms (%lld cudaMalloc)\n",
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_in).count(), g_device_allocs - allocs_in);
     h->seed = seed; h->chain_offset = chain_id_offset;
     const int V = h->V;
     const size_t nmc = (size_t)n_chains * V;
@@ -1098,15 +1141,17 @@ int ssps_init_chains(ssps_handle* h, int32_t n_chains, uint64_t seed, uint32_t c
         CK(cudaStreamSynchronize(h->stream));
         int bound = h->kcap;
         const char* why = "max_indegree";
-        if (h->is_poly) {
-            // interaction columns: the widest design a set of kmax parents needs must fit the from-scratch scorer
-            if (kmax > SSPS_POLY_KMAX || poly_width(kmax, h->cfg.regression_deg) < 0) { bound = std::min(bound, SSPS_POLY_KMAX); why = "the interaction-column scorer's limit"; }
+        if (h->is_poly && kmax > SSPS_POLY_KW) {
+            // interaction columns: sets of more than 64 parents are scored only when their design is saturated (closed form)
+            int m = 0;
+            if (poly_class(SSPS_POLY_KW + 1, h->cfg.regression_deg, h->n, m) != PC_SAT) { bound = std::min(bound, SSPS_POLY_KW); why = "the interaction-column scorer's limit for designs narrower than n - 1 columns"; }
         }
-        if (kmax > bound || (h->is_poly && poly_width(kmax, h->cfg.regression_deg) < 0)) {
+        if (trace)
+            fprintf(stderr, "[ssps trace] init_chains: total %.2f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_in).count());
+        if (kmax > bound) {
             h->n_chains = 0;
-            return fail(SSPS_ERR_INDEGREE, "an initial parent set has %d members, above %s (%d%s); lower the prior's in-degree "
-                        "(--large-indeg) or raise max_indegree", kmax, why, bound,
-                        h->is_poly ? ", or fewer if the design would exceed the column limit" : "");
+            return fail(SSPS_ERR_INDEGREE, "an initial parent set has %d members, above %s (%d); lower the prior's in-degree "
+                        "(--large-indeg) or raise max_indegree", kmax, why, bound);
         }
     }
     return SSPS_OK;
@@ -1522,6 +1567,39 @@ int ssps_measure_fp64_peak(ssps_handle* h, double* tflops) {
     }
     cudaEventDestroy(a); cudaEventDestroy(b);
     *tflops = best;
+    return SSPS_OK;
+}
+
+int ssps_measure_gather_peak(ssps_handle* h, int64_t table_bytes, double* l1_gbs, double* l2_gbs, double* smem_gbs) {
+    CKS(bind(h));
+    if (table_bytes < 8) return fail(SSPS_ERR_INVALID, "ssps_measure_gather_peak: table_bytes < 8");
+    const unsigned n_elems = (unsigned)std::min<int64_t>(table_bytes / 8, (int64_t)1 << 28);
+    const int block = 256, grid = h->sm_count * 8, iters = 1 << 12;
+    DevBuf<double> table, out;
+    CK(table.alloc(n_elems)); CK(out.alloc((size_t)grid * block));
+    CK(cudaMemsetAsync(table.p, 0, table.bytes(), h->stream));
+    cudaEvent_t a, b;
+    CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+    double* res[3] = {l1_gbs, l2_gbs, smem_gbs};
+    for (int mode = 0; mode < 3; ++mode) {
+        if (!res[mode]) continue;
+        double best = 0.0;
+        for (int rep = 0; rep < 4; ++rep) {
+            CK(cudaEventRecord(a, h->stream));
+            if (mode == 0) gather_peak_kernel<0><<<grid, block, 0, h->stream>>>(table.p, n_elems, iters, out.p);
+            else if (mode == 1) gather_peak_kernel<1><<<grid, block, 0, h->stream>>>(table.p, n_elems, iters, out.p);
+            else gather_peak_kernel<2><<<grid, block, 0, h->stream>>>(table.p, n_elems, iters, out.p);
+            CK(cudaEventRecord(b, h->stream));
+            CKS(launch_ok(h, "gather_peak"));
+            CK(cudaEventSynchronize(b));
+            float ms = 0;
+            CK(cudaEventElapsedTime(&ms, a, b));
+            const double bytes = 8.0 * 8.0 * (double)iters * (double)grid * block;
+            if (rep > 0) best = std::max(best, bytes / (ms * 1e-3) / 1e9);
+        }
+        *res[mode] = best;
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b);
     return SSPS_OK;
 }
 

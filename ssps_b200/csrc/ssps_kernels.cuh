@@ -498,3 +498,40 @@ __global__ void __launch_bounds__(256) dfma_peak_kernel(double* out, int iters) 
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Gather-bandwidth microbenchmarks (roofline denominators of SURVEY 8d's `achieved_gather`): random 8-byte loads
+// from a table of the size of G and R (160 kB at V = 100), eight independent loads in flight per thread.
+//   MODE 0  ld.global.nc  (the kernel's __ldg path: L1-resident table)
+//   MODE 1  ld.global.cg  (cached in L2 only: the L2-resident figure)
+//   MODE 2  shared memory (the table's first 48 kB staged in shared memory)
+// The figure returned is USEFUL bytes (8 per load) per second, the same unit as the kernel's gathered bytes.
+// ------------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(256) gather_peak_kernel(const double* __restrict__ table, unsigned n_elems, int iters, double* __restrict__ out) {
+    __shared__ double sh[MODE == 2 ? 6144 : 1];
+    unsigned ne = n_elems;
+    if (MODE == 2) {
+        ne = n_elems < 6144u ? n_elems : 6144u;
+        for (unsigned e = threadIdx.x; e < ne; e += blockDim.x) sh[e] = table[e];
+        __syncthreads();
+    }
+    unsigned s[8];
+    double acc[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { s[u] = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 40503u * (u + 1); acc[u] = 0.0; }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            s[u] = s[u] * 1664525u + 1013904223u;
+            const unsigned idx = __umulhi(s[u], ne);
+            if (MODE == 0) acc[u] += __ldg(table + idx);
+            else if (MODE == 1) acc[u] += __ldcg(table + idx);
+            else acc[u] += sh[idx];
+        }
+    }
+    double r = 0.0;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) r += acc[u];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}

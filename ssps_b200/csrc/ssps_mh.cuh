@@ -188,10 +188,26 @@ struct Stage {
     __device__ __forceinline__ int idof(int a) const { return (int)(id[a] & 0xffffu); }
 };
 
+// Entry e of a Stage's factor rows / w vector.  SH = the Stage is the warp's shared-memory one: the accesses index the
+// ssps_smem symbol (LDS / STS); otherwise plain pointers into the warp's global scratch.
+extern __shared__ double ssps_smem[];
+template <bool SH>
+struct StageAcc {
+    double* tp; double* wp; unsigned toff, woff;
+    __device__ __forceinline__ explicit StageAcc(const Stage& T) : tp(T.t), wp(T.tw), toff(SH ? (unsigned)(T.t - ssps_smem) : 0u), woff(SH ? (unsigned)(T.tw - ssps_smem) : 0u) {}
+    __device__ __forceinline__ double& t(int e) const { if (SH) return ssps_smem[toff + e]; return tp[e]; }
+    __device__ __forceinline__ double& w(int e) const { if (SH) return ssps_smem[woff + e]; return wp[e]; }
+};
+
 // dynamic shared memory of one CTA: SMALL-tier slots of every thread + one Stage per warp
 #define SSPS_SMEM_DOUBLES (SSPS_ROWLEN(SSPS_KS) * SSPS_BLOCK + (SSPS_BLOCK / 32) * SSPS_ROWLEN(SSPS_KST))
 #define SSPS_SMEM_WORDS (SSPS_KS * SSPS_BLOCK + (SSPS_BLOCK / 32) * SSPS_KST)
 #define SSPS_SMEM_BYTES ((size_t)SSPS_SMEM_DOUBLES * 8 + (size_t)SSPS_SMEM_WORDS * 4 + (size_t)(SSPS_BLOCK / 32) * SSPS_KST * 2 + (size_t)SSPS_KS * SSPS_BLOCK)
+
+// The CTA's dynamic shared memory.  Device functions that work on a slot of it index THIS symbol (offset = pointer - ssps_smem):
+// the compiler then knows the address space and emits LDS / STS; through a `double*` parameter the same accesses are generic
+// LD / ST with a descriptor set up before each (measured on the BIG-tier refactorisation: 24 instructions per inner iteration).
+extern __shared__ double ssps_smem[];
 
 struct Lane {
     double lam, somc, ip, nrmf;      // nrmf: screening value of the prior normaliser at lam
@@ -716,7 +732,9 @@ template <bool VERIFY>
 __device__ __noinline__ int mid_move(const SspsDev& P, const int child, const StepDraws& d, const Move& mv, Lane& L, const SmallAcc& S, const BigRef B,
                                      double* F, const KCtx& C, const int rel_now, int& kn_out) {
     const int V = P.V, k = L.k;
-    const uint32_t* Fid = (const uint32_t*)(F + SSPS_ROWLEN(SSPS_KM));      // id | rel << 16, arrival order (the CURRENT set throughout)
+    const unsigned foff = (unsigned)(F - ssps_smem);                        // F is a slot of the warp's shared-memory Stage
+#define FS(e) ssps_smem[foff + (e)]
+    const uint32_t* Fid = (const uint32_t*)(ssps_smem + foff + SSPS_ROWLEN(SSPS_KM));      // id | rel << 16, arrival order (the CURRENT set throughout)
     const uint16_t* Frk = (const uint16_t*)(Fid + SSPS_KM);                 // sorted ranks
 #define FID(b) ((int)(Fid[b] & 0xffffu))
     const int action = mv.action, a_ord = mv.a_ord, r_ord = mv.r_ord;
@@ -746,10 +764,10 @@ __device__ __noinline__ int mid_move(const SspsDev& P, const int child, const St
     if (has_add) { omc_add = __ldg(omc_i + j_add); dprior = -L.lam * omc_add; }
     if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
 
-    double* Fw = F + SSPS_TRI(SSPS_KM);
+#define FW(e) FS(SSPS_TRI(SSPS_KM) + (e))
     double q_new = 0.0;
     #pragma unroll 1
-    for (int m = 0; m < p && m < kr; ++m) q_new = fma(Fw[m], Fw[m], q_new);
+    for (int m = 0; m < p && m < kr; ++m) q_new = fma(FW(m), FW(m), q_new);
     // rows [p, kn) of the proposed set: old slots p + 1 .. k - 1 (entries left of column p are the cached ones), then the
     // arriving parent's row (position kr, nothing cached) -- one loop, one copy of the code
 #pragma unroll 1
@@ -760,25 +778,24 @@ __device__ __noinline__ int mid_move(const SspsDev& P, const int child, const St
         const double* __restrict__ Ga = P.G + (size_t)ja * V;
         const double gaa = __ldg(Ga + ja);
         double d2 = gaa, t = __ldg(Ri + ja);
-        const double* olda = F + SSPS_TRI(a + 1);
-        double* xa = F + SSPS_TRI(a);
+        const int olda = SSPS_TRI(a + 1), xa = SSPS_TRI(a);
 SSPS_UNROLL_MID
-        for (int b = 0; b < c0; ++b) { const double l = olda[b]; xa[b] = l; d2 = fma(-l, l, d2); t = fma(-l, Fw[b], t); }
+        for (int b = 0; b < c0; ++b) { const double l = FS(olda + b); FS(xa + b) = l; d2 = fma(-l, l, d2); t = fma(-l, FW(b), t); }
 SSPS_UNROLL_MID
-        for (int b = c0; b < a; ++b) xa[b] = __ldg(Ga + FID(b + (b >= p ? 1 : 0)));     // the gathers first, back to back: what follows is a dependent chain
+        for (int b = c0; b < a; ++b) FS(xa + b) = __ldg(Ga + FID(b + (b >= p ? 1 : 0)));     // the gathers first, back to back: what follows is a dependent chain
 #pragma unroll 1
         for (int b = c0; b < a; ++b) {
-            const double* xb = F + SSPS_TRI(b);
-            double s = xa[b];
+            const int xb = SSPS_TRI(b);
+            double s = FS(xa + b);
 SSPS_UNROLL_MID
-            for (int m = 0; m < b; ++m) s = fma(-xa[m], xb[m], s);
-            const double l = s * xb[b];
-            xa[b] = l; d2 = fma(-l, l, d2); t = fma(-l, Fw[b], t);
+            for (int m = 0; m < b; ++m) s = fma(-FS(xa + m), FS(xb + m), s);
+            const double l = s * FS(xb + b);
+            FS(xa + b) = l; d2 = fma(-l, l, d2); t = fma(-l, FW(b), t);
         }
         double inv = 0.0, w = 0.0;
         if (d2 > SSPS_PIVOT_TOL * gaa) { inv = inv_sqrt_ieee(d2); w = t * inv; }
         else if (d2 != d2 || gaa != gaa) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; }
-        xa[a] = inv; Fw[a] = w;
+        FS(xa + a) = inv; FW(a) = w;
         q_new = fma(w, w, q_new);
     }
     const double ip_new = C.yty - P.shrink * q_new;
@@ -814,10 +831,10 @@ SSPS_UNROLL_MID
             int r = (int)Frk[oa];
             r -= (r > rp) ? 1 : 0;
             S.W(a) = Fid[oa]; S.set_rank(a, r);
-            const double* row = F + SSPS_TRI(a);
+            const int row = SSPS_TRI(a);
             #pragma unroll 1
-            for (int m = 0; m <= a; ++m) S.d[(SSPS_TRI(a) + m) * SSPS_BLOCK] = row[m];
-            S.Wv(a) = Fw[a];
+            for (int m = 0; m <= a; ++m) S.d[(SSPS_TRI(a) + m) * SSPS_BLOCK] = FS(row + m);
+            S.Wv(a) = FW(a);
         }
         L.mode = MODE_SMALL;
         return 1;
@@ -836,14 +853,16 @@ SSPS_UNROLL_MID
     double* __restrict__ fw = B.fw();
     #pragma unroll 1
     for (int a = p; a < kn; ++a) {      // recomputed rows over the arena rows (proposed set's coordinates)
-        const double* xa = F + SSPS_TRI(a);
+        const int xa = SSPS_TRI(a);
         double* __restrict__ dst = B.f + SSPS_TRI(a);
         #pragma unroll 1
-        for (int m = 0; m <= a; ++m) dst[m] = xa[m];
-        fw[a] = Fw[a];
+        for (int m = 0; m <= a; ++m) dst[m] = FS(xa + m);
+        fw[a] = FW(a);
     }
     return 1;
 #undef FID
+#undef FS
+#undef FW
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -937,101 +956,167 @@ __device__ __forceinline__ void tri_decode(const int idx, int& u, int& v) {
 
 // Factor after the removal of arrival slot p of k: rows p .. k-2 of the reduced set (stage rows p+1 .. k-1;
 // T.id already holds the reduced list).  q_in = sum of w_m^2 over m < p; returns q over all k - 1 rows.
-// The trailing triangle is spread over the lanes pair by pair (a, c), c <= a, numbered from the LAST row
-// upwards, so that the pairs still alive at step b are always a prefix of the lane's list.
-__device__ __noinline__ double fac_remove(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int k, const int p,
-                                          double q, const int lane
+//
+// Phase A: every entry (a, c), p <= c <= a, of the trailing triangle is seeded with  G_ac - sum_{m<p} l_am l_cm  (the
+// unchanged columns, ascending m), the diagonal pair of row a also with  t_a = r_a - sum_{m<p} l_am w_m.  The pairs are
+// spread over the lanes; the G / R gathers of all of a lane's pairs are issued first, back to back (an L2 round trip
+// each when they miss: one latency instead of one per pair).
+// Phase B: right-looking elimination of the trailing triangle, a lane per ROW.  Step b: every lane forms the pivot
+// (1 / d_b, w_b) from d_b^2 and t_b, which the owner of row b handed to the warp by shuffle at the end of the previous
+// step; lane a scales its entry l_ab (loaded BEFORE the 1/sqrt chain, so the load hides behind it) and the owner of
+// row b + 1 forms the next pivot's inputs at once -- the dependent chain from one pivot to the next is
+// 1/sqrt -> multiply -> fma -> shuffle and nothing else.  Then the column of scaled entries goes round by shuffle: for
+// c = b + 1 ..: l_cb comes from lane c, and lane a subtracts l_ab l_cb from its entry (a, c).  No barrier, no shared-
+// memory traffic other than a lane's own row.  Every entry receives its terms in ascending b through fma -- the bits
+// of the row-by-row factorisation.  (Round 1: three barriers per step, 700 cycles; round 2, first version: one barrier,
+// every lane re-reading and re-scaling the other rows' column entries from shared memory: 1 680 cycles per step
+// measured in the time-to-convergence regime, 68 % of a BIG-tier pass.)
+// Rows beyond the first 32 of the trailing block (sets of more than ~40 parents) take the general path below.
+template <bool SH>
+__device__ __noinline__ double fac_remove_impl(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int k, const int p,
+                                               double q, const int lane
 #ifdef SSPS_PROFILE_BIG
-                                          , unsigned long long* prof
+                                               , unsigned long long* prof
 #endif
-                                          ) {
+                                               ) {
     const int V = P.V, kr = k - 1, nt = kr - p;
-    double* t = T.t; double* tw = T.tw;
+    const StageAcc<SH> A(T);
     if (nt <= 0) return q;
 #ifdef SSPS_PROFILE_BIG
     const long long tp0_ = clock64();
 #endif
-#define SROW(a) (t + SSPS_TRI((a) + 1))      /* a >= p: stage row a + 1 */
+#define SROW(a) SSPS_TRI((a) + 1)            /* a >= p: stage row a + 1 (offset of its first entry) */
 #define SCOL(c) ((c) + 1)                    /* c >= p: stage column c + 1 */
-    // partial sums over the unchanged columns m < p; the diagonal pair of row a also carries t_a
-    for (int idx = lane; idx < nt * (nt + 1) / 2; idx += 32) {
+    // ---- phase A ----
+    const int npairs = nt * (nt + 1) / 2;
+    for (int idx = lane; idx < npairs; idx += 32) {         // gathers first
         int u, v;
         tri_decode(idx, u, v);
         const int a = kr - 1 - u, c = kr - 1 - v;
         const int ja = T.idof(a);
-        double* ra = SROW(a);
-        const double* rc = SROW(c);
-        double x = __ldg(P.G + (size_t)ja * V + T.idof(c));
+        A.t(SROW(a) + SCOL(c)) = __ldg(P.G + (size_t)ja * V + T.idof(c));
+        if (c == a) A.w(a + 1) = __ldg(Ri + ja);
+    }
+    for (int idx = lane; idx < npairs; idx += 32) {         // the lane re-reads its own seeds: no barrier needed
+        int u, v;
+        tri_decode(idx, u, v);
+        const int a = kr - 1 - u, c = kr - 1 - v;
+        const int ra = SROW(a), rc = SROW(c);
+        double x = A.t(ra + SCOL(c));
         if (c == a) {
-            double xt = __ldg(Ri + ja);
-            for (int m = 0; m < p; ++m) { const double l = ra[m]; x = fma(-l, l, x); xt = fma(-l, tw[m], xt); }
-            tw[a + 1] = xt;
+            double xt = A.w(a + 1);
+            for (int m = 0; m < p; ++m) { const double l = A.t(ra + m); x = fma(-l, l, x); xt = fma(-l, A.w(m), xt); }
+            A.w(a + 1) = xt;
         } else {
-            for (int m = 0; m < p; ++m) x = fma(-ra[m], rc[m], x);
+            for (int m = 0; m < p; ++m) x = fma(-A.t(ra + m), A.t(rc + m), x);
         }
-        ra[SCOL(c)] = x;
+        A.t(ra + SCOL(c)) = x;
     }
     __syncwarp();
-    // Trailing update, a lane per row (lane owns rows a = p + lane, + 32, ...).  Step b: every lane forms the pivot (1 / d_b, w_b)
-    // from d_b^2 and t_b, which the owner of row b handed to the warp by shuffle at the end of the previous step -- so the
-    // dependent chain from one pivot to the next is  1/sqrt -> one multiply -> one fma -> shuffle  and nothing else; then lane a
-    // scales its entry of column b and subtracts its products from the entries (a, c), b < c <= a, of its own row, reading the
-    // still UNSCALED column b of the other rows (x * inv gives the bits the owner will store).  Every entry receives its terms in
-    // ascending b through fma -- the bits of the row-by-row factorisation.  ONE warp barrier per step: the scaled column goes
-    // to shared memory after it, when nobody reads the unscaled one any more.  (Round 1: three barriers per step and the pivot read
-    // back from shared memory, 700 cycles per step; 65 % of a BIG-tier pass was spent here.)
 #ifdef SSPS_PROFILE_BIG
     const long long tp1_ = clock64();
 #endif
-    double gd = 0.0;                                    // G_aa of this lane's first row: the pivots' tolerance reference
-    if (p + lane < kr) { const int ja = T.idof(p + lane); gd = __ldg(P.G + (size_t)ja * V + ja); }
-    double d2 = SROW(p)[SCOL(p)], tb = tw[p + 1];
-    for (int b = p; b < kr; ++b) {
-        double gbb = __shfl_sync(SSPS_FULL, gd, (b - p) & 31);
-        if (b - p >= 32) { const int jb = T.idof(b); gbb = __ldg(P.G + (size_t)jb * V + jb); }
-        double inv, wb;
-        chol_pivot(d2, gbb, tb, inv, wb, q);
-        // the next pivot's inputs first: the owner of row b + 1 needs one product
-        const int own = (b + 1 - p) & 31;
-        double d2n = 0.0, tn = 0.0;
-        if (b + 1 < kr && lane == own) {
-            const double* rn = SROW(b + 1);
-            const double l = rn[SCOL(b)] * inv;
-            d2n = fma(-l, l, rn[SCOL(b + 1)]);
-            tn = fma(-l, wb, tw[b + 2]);
-        }
-        d2n = __shfl_sync(SSPS_FULL, d2n, own);
-        tn = __shfl_sync(SSPS_FULL, tn, own);
-        double lab_keep[SSPS_KU];
-#pragma unroll
-        for (int u = 0; u < SSPS_KU; ++u) {
-            lab_keep[u] = 0.0;
-            const int a = p + lane + 32 * u;
-            if (a > b && a < kr) {
-                double* ra = SROW(a);
-                const double lab = ra[SCOL(b)] * inv;
-                for (int c = b + 1; c < a; ++c) ra[SCOL(c)] = fma(-lab, SROW(c)[SCOL(b)] * inv, ra[SCOL(c)]);
-                ra[SCOL(a)] = fma(-lab, lab, ra[SCOL(a)]);
-                tw[a + 1] = fma(-lab, wb, tw[a + 1]);
-                lab_keep[u] = lab;
+    // ---- phase B ----
+    if (nt <= 32) {
+        const int a = p + lane;
+        const bool mine = a < kr;
+        const int ra = SROW(mine ? a : p);
+        double gd = 0.0, tw_a = 0.0;
+        if (mine) { const int ja = T.idof(a); gd = __ldg(P.G + (size_t)ja * V + ja); tw_a = A.w(a + 1); }
+        double d2 = A.t(SROW(p) + SCOL(p)), tb = A.w(p + 1);
+        const int a_eff = mine ? a : -1;                    // rows of the other lanes: no entry passes  c <= a_eff
+        for (int b = p; b < kr; ++b) {
+            const bool below = a_eff > b;
+            int rb = ra + SCOL(b);                                              // entry (a, b); (a, b + 1), .. follow
+            const double xab = below ? A.t(rb) : 0.0;                           // before the 1/sqrt chain
+            const double xnn = (a_eff == b + 1) ? A.t(rb + 1) : 0.0;            // the next diagonal, too
+            const double gbb = __shfl_sync(SSPS_FULL, gd, b - p);
+            double inv, wb;
+            chol_pivot(d2, gbb, tb, inv, wb, q);
+            const double lab = xab * inv;                                       // 0 for the lanes at or above the pivot row
+            const double nlab = -lab;
+            tw_a = fma(nlab, wb, tw_a);
+            // the next pivot's inputs, from the owner of row b + 1 (its diagonal entry is updated again, identically, in the loop below)
+            const double d2n = __shfl_sync(SSPS_FULL, fma(nlab, lab, xnn), (b + 1 - p) & 31);
+            const double tn = __shfl_sync(SSPS_FULL, tw_a, (b + 1 - p) & 31);
+            const int a_lim = below ? a : -1;
+            int src = b + 1 - p;
+#pragma unroll 4
+            for (int c = b + 1; c < kr; ++c, ++src) {
+                const double lcb = __shfl_sync(SSPS_FULL, lab, src);
+                ++rb;
+                if (c <= a_lim) A.t(rb) = fma(nlab, lcb, A.t(rb));
             }
+            rb = ra + SCOL(b);
+            if (below) A.t(rb) = lab;
+            if (a_eff == b) { A.t(rb) = inv; A.w(b + 1) = wb; }
+            d2 = d2n; tb = tn;
         }
-        __syncwarp();                               // nobody reads the unscaled column b any more
+        __syncwarp();
+    } else {
+        // general path: a lane owns rows p + lane + 32 u; one warp barrier per step (the scaled column goes to shared memory after it)
+        double gd = 0.0;                                    // G_aa of this lane's first row: the pivots' tolerance reference
+        if (p + lane < kr) { const int ja = T.idof(p + lane); gd = __ldg(P.G + (size_t)ja * V + ja); }
+        double d2 = A.t(SROW(p) + SCOL(p)), tb = A.w(p + 1);
+        for (int b = p; b < kr; ++b) {
+            double gbb = __shfl_sync(SSPS_FULL, gd, (b - p) & 31);
+            if (b - p >= 32) { const int jb = T.idof(b); gbb = __ldg(P.G + (size_t)jb * V + jb); }
+            double inv, wb;
+            chol_pivot(d2, gbb, tb, inv, wb, q);
+            const int own = (b + 1 - p) & 31;
+            double d2n = 0.0, tn = 0.0;
+            if (b + 1 < kr && lane == own) {
+                const int rn = SROW(b + 1);
+                const double l = A.t(rn + SCOL(b)) * inv;
+                d2n = fma(-l, l, A.t(rn + SCOL(b + 1)));
+                tn = fma(-l, wb, A.w(b + 2));
+            }
+            d2n = __shfl_sync(SSPS_FULL, d2n, own);
+            tn = __shfl_sync(SSPS_FULL, tn, own);
+            double lab_keep[SSPS_KU];
 #pragma unroll
-        for (int u = 0; u < SSPS_KU; ++u) {
-            const int a = p + lane + 32 * u;
-            if (a > b && a < kr) SROW(a)[SCOL(b)] = lab_keep[u];
+            for (int u = 0; u < SSPS_KU; ++u) {
+                lab_keep[u] = 0.0;
+                const int a = p + lane + 32 * u;
+                if (a > b && a < kr) {
+                    const int ra = SROW(a);
+                    const double lab = A.t(ra + SCOL(b)) * inv;
+                    for (int c = b + 1; c < a; ++c) A.t(ra + SCOL(c)) = fma(-lab, A.t(SROW(c) + SCOL(b)) * inv, A.t(ra + SCOL(c)));
+                    A.t(ra + SCOL(a)) = fma(-lab, lab, A.t(ra + SCOL(a)));
+                    A.w(a + 1) = fma(-lab, wb, A.w(a + 1));
+                    lab_keep[u] = lab;
+                }
+            }
+            __syncwarp();                               // nobody reads the unscaled column b any more
+#pragma unroll
+            for (int u = 0; u < SSPS_KU; ++u) {
+                const int a = p + lane + 32 * u;
+                if (a > b && a < kr) A.t(SROW(a) + SCOL(b)) = lab_keep[u];
+            }
+            if (lane == 0) { A.t(SROW(b) + SCOL(b)) = inv; A.w(b + 1) = wb; }
+            d2 = d2n; tb = tn;
         }
-        if (lane == 0) { SROW(b)[SCOL(b)] = inv; tw[b + 1] = wb; }
-        d2 = d2n; tb = tn;
+        __syncwarp();
     }
-    __syncwarp();
 #ifdef SSPS_PROFILE_BIG
     if (lane == 0) { atomicAdd(prof + 28, (unsigned long long)(tp1_ - tp0_)); atomicAdd(prof + 29, (unsigned long long)(clock64() - tp1_)); atomicAdd(prof + 30, (unsigned long long)nt); atomicAdd(prof + 31, 1ull); }
 #endif
 #undef SROW
 #undef SCOL
     return q;
+}
+
+__device__ __forceinline__ double fac_remove(const SspsDev& P, const double* __restrict__ Ri, const Stage T, const int k, const int p,
+                                             double q, const int lane
+#ifdef SSPS_PROFILE_BIG
+                                             , unsigned long long* prof
+#endif
+                                             ) {
+#ifdef SSPS_PROFILE_BIG
+    return __isShared(T.t) ? fac_remove_impl<true>(P, Ri, T, k, p, q, lane, prof) : fac_remove_impl<false>(P, Ri, T, k, p, q, lane, prof);
+#else
+    return __isShared(T.t) ? fac_remove_impl<true>(P, Ri, T, k, p, q, lane) : fac_remove_impl<false>(P, Ri, T, k, p, q, lane);
+#endif
 }
 
 // Row kr of the proposed set's factor: parent j appended to its kr rows (forward substitution, lane owns
@@ -1266,7 +1351,7 @@ __device__ __noinline__ Lane task_settle(const SspsDev& P, const int child, Lane
 template <class Source, bool VERIFY>
 __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(const __grid_constant__ SspsDev P, const __grid_constant__ ChainState st,
                                                                               const __grid_constant__ MhParams prm, const __grid_constant__ Source src) {
-    extern __shared__ double smem_d[];
+    double* const smem_d = ssps_smem;
     const int lane = threadIdx.x & 31;
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
     SmallAcc S;

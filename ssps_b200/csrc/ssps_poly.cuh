@@ -1,35 +1,105 @@
-// ssps_poly.cuh -- regression_deg != 1: interaction columns (sm_100a).
+// ssps_poly.cuh -- regression_deg >= 2: interaction columns (sm_100a).
 //
 // Reference semantics (paths relative to the gitter-lab/ssps checkout):
 //   compute_B_col / construct_B   SSPS/src/dbn_distributions.jl:168-194
 //       for deg = 1..regression_deg, for each Combinatorics.combinations(sorted S, deg) (lexicographic):
 //       elementwise product of the RAW Xminus columns, then (x - mean) / std (corrected, ddof 1)
-//   compute_lml                   SSPS/src/dbn_distributions.jl:235-248
-//       lml = -1/2 width log(1 + n) - 1/2 n log( y'y - n/(n+1) |P_B y|^2 )
+//   safe_solve / compute_lml      SSPS/src/dbn_distributions.jl:201-248
+//       lml = -1/2 width log(1 + n) - 1/2 n log( y'y - n/(n+1) |P_B y|^2 ),  P_B = projection on span(B)
+//       (Julia's `\` on a non-square B is pivoted QR with a rank cut: ANY width is legal, also width > n)
 //   regression_deg <= 0 (the CLI default -1, "full") builds an EMPTY design in the reference (quirk Q2):
-//       width = 0, lml = -1/2 n log(y'y) for every parent set -- reproduced as is.
+//       that case runs through the degree-1 cached-factor kernel with q = 0 (ssps_capi.cu), not through this file.
+//   "full" of BASELINE.json's config C5 = regression_deg >= |S| (all non-empty product subsets, Hill's 'full').
 //
-// The product columns are re-standardised per set, so their Gram matrix cannot be tabulated once
-// like G = Z'Z of the degree-1 path: every proposal is scored FROM SCRATCH.  One thread scores one
-// set: two passes over the n lagged rows (column means; then the Gram matrix of the centred columns
-// and their products with y), a scaling to the standardised design, and the same pivot-skipping
-// Cholesky as the degree-1 path (column order = the reference's).  Scratch lives in a global arena,
-// interleaved across threads so that a warp touching the same logical index is coalesced.
+// The product columns are re-standardised per set, so their Gram matrix cannot be tabulated once like G = Z'Z of
+// the degree-1 path: every proposal is scored FROM SCRATCH.  Three classes of (k, deg, n), by design width
+// m = sum_{d <= min(deg, k)} C(k, d):
 //
-// Cost per scored set: n (m + m (m + 1) / 2 + m) multiply-adds for m = sum_{d <= deg} C(k, d) columns
-// (SURVEY 8d); the arithmetic is fp64 on the DFMA pipe.
+//   SATURATED  m >= n - 1.  The columns are centred, so they span at most the (n - 1)-dimensional centred subspace,
+//              which holds y: the projection is y itself, |P_B y|^2 = y'y, and
+//                  lml = -1/2 m log(1 + n) - 1/2 n log( y'y / (n + 1) )
+//              in closed form -- no design is built ("|S| >= n - 1 the projection saturates").  This is what
+//              the reference's rank-cut QR returns for a design of full row rank; it removes every limit on k for
+//              such sets (2^k - 1 >= n - 1 at "full" from k = log2 n on; the reference itself cannot allocate B there).
+//   THREAD     m <= 48, k <= 12: one thread scores one set (poly_score_set): two passes over the n lagged rows (column
+//              means; Gram matrix of the centred columns and their products with y), scaling to the standardised
+//              design, and the same pivot-skipping Cholesky as the degree-1 path (column order = the reference's).
+//   WARP       48 < m < n - 1 (k <= 64): the whole warp scores one set (poly_score_warp): a lane owns COLUMNS, every
+//              Gram entry is accumulated by one lane in ascending row order and the Cholesky is right-looking with every
+//              entry receiving its updates in ascending pivot order -- the operation order of the THREAD tier, so the
+//              two tiers return the same bits and the tier choice (a function of k, deg, n alone) is not visible in
+//              the results.  The n m^2 Gram of the product columns is the one place on this path where a single
+//              proposal is large enough for 32 lanes (1e5..1e7 fma).
+//
+// Cost per scored set (deg > 1): n (3 m + m^2 + 2 m) + m^3/3 + 2 m^2 + 2 m flops; fp64 on the DFMA pipe.
 #pragma once
 #include "ssps_kernels.cuh"
 
-#define SSPS_POLY_KMAX 12          // parents per set the interaction path handles
-#define SSPS_POLY_MMAX 48          // design columns per set
+#define SSPS_POLY_KMAX 12          // THREAD tier: parents per set
+#define SSPS_POLY_MMAX 48          // THREAD tier: design columns per set
+#define SSPS_POLY_KW 64            // WARP tier: parents per set (64-bit column masks)
+#define SSPS_POLY_KLIST 128        // per-thread parent lists of the MH kernel (= the library's hard max_indegree ceiling)
+
+enum { PC_NONE = 0, PC_EMPTY = 1, PC_SAT = 2, PC_THREAD = 3, PC_WARP = 4, PC_REFUSE = 5 };
 
 struct PolyDev {
     const double* Xminus;          // n x V column-major, RAW
     const double* Y;               // n x V column-major, standardised
-    int deg;                       // regression_deg (<= 0: empty design)
+    int deg;                       // regression_deg (>= 2 on this path)
 };
 
+// design width sum_{d = 1..min(deg, k)} C(k, d), exact while <= limit; limit + 1 as soon as it exceeds the limit
+__host__ __device__ inline long long poly_width_capped(int k, int deg, long long limit) {
+    long long m = 0, c = 1;
+    const int dmax = deg < k ? deg : k;
+    for (int d = 1; d <= dmax; ++d) {
+        c = c * (long long)(k - d + 1) / (long long)d;      // exact: c is C(k, d - 1) <= limit, times at most k
+        if (c > limit) return limit + 1;
+        m += c;
+        if (m > limit) return limit + 1;
+    }
+    return m;
+}
+// the same width as a double (exact up to 2^53; the reference's Int64 sum overflows long before it could build such a B)
+__host__ __device__ inline double poly_width_d(int k, int deg) {
+    double m = 0.0, c = 1.0;
+    const int dmax = deg < k ? deg : k;
+    for (int d = 1; d <= dmax; ++d) { c = c * (double)(k - d + 1) / (double)d; m += c; }
+    return m;
+}
+// class of a set of k parents; m_out = its width when it is scored numerically (THREAD / WARP)
+__host__ __device__ inline int poly_class(int k, int deg, int n, int& m_out) {
+    m_out = 0;
+    if (deg <= 0 || k == 0) return PC_EMPTY;
+    const long long lim = (long long)n - 2;
+    const long long m = poly_width_capped(k, deg, lim < 0 ? 0 : lim);
+    if (m > lim) return PC_SAT;
+    m_out = (int)m;
+    if (m <= SSPS_POLY_MMAX && k <= SSPS_POLY_KMAX) return PC_THREAD;
+    return k <= SSPS_POLY_KW ? PC_WARP : PC_REFUSE;
+}
+// widest numerically scored design any set of at most kcap parents can have (sizes the WARP tier's scratch)
+inline int poly_max_scored_width(int kcap, int deg, int n) {
+    int best = 0;
+    for (int k = 1; k <= kcap && k <= SSPS_POLY_KW; ++k) {
+        int m = 0;
+        const int c = poly_class(k, deg, n, m);
+        if (c == PC_THREAD || c == PC_WARP) best = m > best ? m : best;
+    }
+    return best;
+}
+
+// closed forms
+__device__ __forceinline__ double poly_lml_empty(const SspsDev& P, const int child) { return -0.5 * P.dn * log(__ldg(P.yty + child)); }
+__device__ __forceinline__ double poly_lml_saturated(const SspsDev& P, const PolyDev& Q, const int child, const int k) {
+    const double yty = __ldg(P.yty + child);
+    const double ip = yty - P.shrink * yty;             // |P_B y|^2 = y'y
+    return -0.5 * poly_width_d(k, Q.deg) * P.log1pn - 0.5 * P.dn * log(ip);
+}
+
+// ------------------------------------------------------------------------------------------------
+// THREAD tier
+// ------------------------------------------------------------------------------------------------
 // per-thread scratch, element e at d[e * stride]
 struct PolyScratch {
     double* d; int stride;
@@ -42,31 +112,19 @@ struct PolyScratch {
 };
 #define SSPS_POLY_SCRATCH_DOUBLES (3 * SSPS_POLY_MMAX + SSPS_TRI(SSPS_POLY_MMAX))
 
-// number of design columns: sum_{d = 1..min(deg, k)} C(k, d); -1 if it exceeds SSPS_POLY_MMAX
-__host__ __device__ inline int poly_width(int k, int deg) {
-    int m = 0;
-    long long c = 1;
-    const int dmax = deg < k ? deg : k;
-    for (int d = 1; d <= dmax; ++d) {
-        c = c * (k - d + 1) / d;
-        if (c > SSPS_POLY_MMAX) return -1;
-        m += (int)c;
-        if (m > SSPS_POLY_MMAX) return -1;
-    }
-    return m;
-}
-
-// bit masks (over positions of the sorted set) of the design columns, in the reference's order
-__device__ inline int poly_masks(int k, int deg, unsigned short* masks) {
+// bit masks (over positions of the sorted set) of the design columns, in the reference's order:
+// for d = 1..min(deg, k), Combinatorics.combinations(S, d) in lexicographic order
+template <class Mask, class Emit>
+__device__ inline int poly_enumerate(int k, int deg, Emit emit) {
     int m = 0;
     const int dmax = deg < k ? deg : k;
-    int idx[SSPS_POLY_KMAX];
+    int idx[SSPS_POLY_KW];
     for (int d = 1; d <= dmax; ++d) {
         for (int a = 0; a < d; ++a) idx[a] = a;
         for (;;) {
-            unsigned mk = 0;
-            for (int a = 0; a < d; ++a) mk |= 1u << idx[a];
-            masks[m++] = (unsigned short)mk;
+            Mask mk = 0;
+            for (int a = 0; a < d; ++a) mk |= (Mask)1 << idx[a];
+            emit(m++, mk);
             int i = d - 1;
             while (i >= 0 && idx[i] == k - d + i) --i;
             if (i < 0) break;
@@ -77,17 +135,30 @@ __device__ inline int poly_masks(int k, int deg, unsigned short* masks) {
     return m;
 }
 
-// lml(child, S) for the SORTED set S[0..k).  Returns NaN when the set is outside the path's limits
-// (the callers check the limits first and fail loudly).
-__device__ inline double poly_score_set(const SspsDev& P, const PolyDev& Q, const int child, const int* S, const int k,
+// lml(child, S) for the SORTED set S[0..k) of class PC_THREAD with m columns
+__device__ inline double poly_score_set(const SspsDev& P, const PolyDev& Q, const int child, const uint16_t* S, const int k, const int m,
                                         const PolyScratch& sc) {
     const int n = P.n;
     const double yty = P.yty[child];
-    const int m = (Q.deg <= 0) ? 0 : poly_width(k, Q.deg);
-    if (m < 0 || k > SSPS_POLY_KMAX) return __longlong_as_double(0x7ff8000000000000LL);
-    if (m == 0) return -0.5 * P.dn * log(yty);               // empty design (k = 0, or quirk Q2)
     unsigned short masks[SSPS_POLY_MMAX];
-    poly_masks(k, Q.deg, masks);
+    {
+        int idx[SSPS_POLY_KMAX];
+        int c = 0;
+        const int dmax = Q.deg < k ? Q.deg : k;
+        for (int d = 1; d <= dmax; ++d) {
+            for (int a = 0; a < d; ++a) idx[a] = a;
+            for (;;) {
+                unsigned mk = 0;
+                for (int a = 0; a < d; ++a) mk |= 1u << idx[a];
+                masks[c++] = (unsigned short)mk;
+                int i = d - 1;
+                while (i >= 0 && idx[i] == k - d + i) --i;
+                if (i < 0) break;
+                ++idx[i];
+                for (int a = i + 1; a < d; ++a) idx[a] = idx[a - 1] + 1;
+            }
+        }
+    }
     const double* __restrict__ y = Q.Y + (size_t)child * n;
     double xs[SSPS_POLY_KMAX];
     // pass 1: column means
@@ -145,41 +216,226 @@ __device__ inline double poly_score_set(const SspsDev& P, const PolyDev& Q, cons
     return -0.5 * (double)m * P.log1pn - 0.5 * P.dn * log(ip);
 }
 
-// K2 for the interaction path: one thread per (child, S)
-__global__ void poly_score_kernel(SspsDev P, PolyDev Q, int n_sets, const int* __restrict__ child, const int* __restrict__ offsets,
-                                  const int* __restrict__ members, const double* __restrict__ lambda, double* __restrict__ arena,
-                                  double* __restrict__ lml_out, double* __restrict__ lp_out) {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n_sets) return;
-    PolyScratch sc{arena + s, (int)(gridDim.x * blockDim.x)};
-    const int i = child[s], k = offsets[s + 1] - offsets[s];
-    const int* mem = members + offsets[s];
-    int S[SSPS_POLY_KMAX];
-    for (int a = 0; a < k && a < SSPS_POLY_KMAX; ++a) S[a] = mem[a];
-    if (lml_out) lml_out[s] = poly_score_set(P, Q, i, S, k, sc);
-    if (lp_out) {
-        const double lam = lambda[s];
-        double somc = 0.0;
-        for (int a = 0; a < k; ++a) somc += P.omc[(size_t)mem[a] + (size_t)P.V * i];
-        lp_out[s] = -lam * somc - prior_normaliser(P, i, lam);
+// ------------------------------------------------------------------------------------------------
+// WARP tier.  Scratch of one warp (global memory; the working set of one set is n mp + m mp doubles, L1/L2-resident
+// for the widths that occur in a stationary chain): cv[t][c] = the centred product columns (row-major, mp = m rounded
+// up to 32 columns, padding columns zero), g[a][b] = the Gram matrix / the factor in place (b <= a), and a few vectors.
+// ------------------------------------------------------------------------------------------------
+struct PolyWarpScratch {
+    double* base;           // this warp's block
+    int n, mcap_p;          // rows, column capacity (multiple of 32)
+    __device__ __forceinline__ double* cv() const { return base; }                                         // n * mcap_p
+    __device__ __forceinline__ double* g() const { return base + (size_t)n * mcap_p; }                    // mcap_p * mcap_p
+    __device__ __forceinline__ double* vec(int e) const { return g() + (size_t)mcap_p * mcap_p + (size_t)e * mcap_p; }   // e < 4: isd, rhs, gd, colp
+    __device__ __forceinline__ unsigned long long* masks() const { return (unsigned long long*)vec(4); }   // mcap_p
+    __device__ __forceinline__ int* ids() const { return (int*)vec(5); }                                    // SSPS_POLY_KW
+};
+__host__ __device__ inline size_t poly_warp_scratch_doubles(int n, int mcap_p) { return (size_t)n * mcap_p + (size_t)mcap_p * mcap_p + 5 * (size_t)mcap_p + SSPS_POLY_KW; }
+
+// 1 / sqrt(x), IEEE sqrt then IEEE division: the THREAD tier's bits
+__device__ __noinline__ double poly_inv_sqrt(const double x) { return 1.0 / sqrt(x); }
+
+// lml(child, S) for the sorted set W.ids()[0..k) of class PC_WARP with m columns.  All arguments warp-uniform, every lane
+// calls.  Same operation order, same bits as poly_score_set.
+__device__ __noinline__ double poly_score_warp(const SspsDev& P, const PolyDev& Q, const int child, const int k, const int m,
+                                               const PolyWarpScratch& W, const int lane) {
+    const int n = P.n;
+    const int mp = (m + 31) & ~31, nj = mp >> 5;
+    double* cv = W.cv();
+    double* g = W.g();
+    double* isd = W.vec(0);
+    double* rhs = W.vec(1);
+    double* gd = W.vec(2);
+    double* colp = W.vec(3);
+    unsigned long long* masks = W.masks();     // (no __restrict__ on the scratch: lanes hand data to each other through it)
+    const int* ids = W.ids();
+    const double* __restrict__ y = Q.Y + (size_t)child * n;
+
+    if (lane == 0) poly_enumerate<unsigned long long>(k, Q.deg, [&](int c, unsigned long long mk) { masks[c] = mk; });
+    __syncwarp();
+    // pass 1: products and column means (a lane owns columns lane + 32 j; ascending t)
+    for (int j = 0; j < nj; ++j) {
+        const int c = lane + 32 * j;
+        const unsigned long long mk = c < m ? masks[c] : 0ull;
+        double mean = 0.0;
+        for (int t = 0; t < n; ++t) {
+            double pr = 0.0;
+            if (c < m) {
+                pr = 1.0;
+                unsigned long long mm = mk;
+                while (mm) { const int a = __ffsll((long long)mm) - 1; mm &= mm - 1; pr *= __ldg(Q.Xminus + (size_t)ids[a] * n + t); }
+                mean += pr;
+            }
+            cv[(size_t)t * mp + c] = pr;
+        }
+        mean = mean / (double)n;
+        // pass 2: centre; products with y
+        double r = 0.0;
+        if (c < m) {
+            for (int t = 0; t < n; ++t) {
+                const double v = cv[(size_t)t * mp + c] - mean;
+                cv[(size_t)t * mp + c] = v;
+                r = fma(v, __ldg(y + t), r);
+            }
+        }
+        rhs[c] = r;
+    }
+    __syncwarp();
+    // Gram matrix of the centred columns: tiles of 4 rows x (4 x 32) columns, every entry one lane's ascending-t fma chain
+    for (int c0 = 0; c0 < m; c0 += 4) {
+        const int jend = (min(c0 + 3, m - 1) >> 5) + 1;             // column chunks that hold some b <= c
+        for (int jb = 0; jb < jend; jb += 4) {
+            double acc[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[r][j] = 0.0;
+            const double* row = cv;
+            for (int t = 0; t < n; ++t, row += mp) {
+                double bc[4], col[4];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) bc[r] = row[c0 + r];         // c0 + 3 < mp: padding columns are zero
+#pragma unroll
+                for (int j = 0; j < 4; ++j) col[j] = (jb + j < nj) ? row[lane + 32 * (jb + j)] : 0.0;
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[r][j] = fma(bc[r], col[j], acc[r][j]);
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int c = c0 + r, b = lane + 32 * (jb + j);
+                    if (c < m && b <= c) g[(size_t)c * mp + b] = acc[r][j];
+                }
+        }
+    }
+    __syncwarp();
+    // standardise: B_c = centred column / sd_c, sd_c = sqrt(C_cc / (n - 1))
+    for (int c = lane; c < m; c += 32) isd[c] = 1.0 / sqrt(g[(size_t)c * mp + c] / (double)(n - 1));
+    __syncwarp();
+    for (int c = lane; c < m; c += 32) rhs[c] = rhs[c] * isd[c];
+    for (int c = 0; c < m; ++c) {
+        const double ic = isd[c];
+        for (int b = lane; b <= c; b += 32) g[(size_t)c * mp + b] = g[(size_t)c * mp + b] * ic * isd[b];
+    }
+    __syncwarp();
+    for (int c = lane; c < m; c += 32) gd[c] = g[(size_t)c * mp + c];
+    __syncwarp();
+    // pivot-skipping Cholesky, right-looking: entry (a, b) receives  - l_ap l_bp  for p = 0, 1, .. in ascending order through fma
+    // (the diagonal and the rhs entry of row a are entries of that row: d2_a -= l_ap^2, t_a -= l_ap w_p)
+    double q = 0.0;
+    for (int p = 0; p < m; ++p) {
+        const double d2 = g[(size_t)p * mp + p], tt = rhs[p], gaa = gd[p];
+        double inv, w;
+        if (d2 > SSPS_PIVOT_TOL * gaa) { inv = poly_inv_sqrt(d2); w = tt * inv; q = fma(w, w, q); }
+        else if (d2 != d2 || gaa != gaa) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; q = inv; }
+        else continue;                                  // numerically dependent column: l_ap = 0 for every a, nothing to subtract
+        for (int a = p + 1 + lane; a < m; a += 32) colp[a] = g[(size_t)a * mp + p] * inv;
+        __syncwarp();
+        for (int a = p + 1 + lane; a < m; a += 32) rhs[a] = fma(-colp[a], w, rhs[a]);
+        // trailing rows: lanes over b within a row, four rows in flight
+        for (int bb = p + 1; bb < m; bb += 32) {
+            const int b = bb + lane;
+            const double lb = b < m ? colp[b] : 0.0;
+            int a = bb;
+            for (; a + 3 < m; a += 4) {
+                const double l0 = colp[a], l1 = colp[a + 1], l2 = colp[a + 2], l3 = colp[a + 3];
+                double* r0 = g + (size_t)a * mp;
+                if (b <= a) r0[b] = fma(-l0, lb, r0[b]);
+                if (b <= a + 1) r0[mp + b] = fma(-l1, lb, r0[mp + b]);
+                if (b <= a + 2) r0[2 * (size_t)mp + b] = fma(-l2, lb, r0[2 * (size_t)mp + b]);
+                if (b <= a + 3) r0[3 * (size_t)mp + b] = fma(-l3, lb, r0[3 * (size_t)mp + b]);
+            }
+            for (; a < m; ++a) {
+                const double la = colp[a];
+                if (b <= a) g[(size_t)a * mp + b] = fma(-la, lb, g[(size_t)a * mp + b]);
+            }
+        }
+        __syncwarp();
+    }
+    const double ip = __ldg(P.yty + child) - P.shrink * q;
+    return -0.5 * (double)m * P.log1pn - 0.5 * P.dn * log(ip);
+}
+
+// lml of this lane's sorted set S[0..k) whatever its class; warp-collective (every lane calls; dead lanes pass live = false).
+// A PC_REFUSE set (more than SSPS_POLY_KW parents whose design is still narrower than n - 1 rows) returns NaN: the callers refuse
+// such sets before they get here.
+__device__ inline double poly_score_any(const SspsDev& P, const PolyDev& Q, const int child, const uint16_t* S, const int k, const bool live,
+                                        const PolyScratch& sc, const PolyWarpScratch& W, const int lane) {
+    int m = 0;
+    const int cls = live ? poly_class(k, Q.deg, P.n, m) : PC_NONE;
+    double v = __longlong_as_double(0x7ff8000000000000LL);
+    if (cls == PC_EMPTY) v = poly_lml_empty(P, child);
+    else if (cls == PC_SAT) v = poly_lml_saturated(P, Q, child, k);
+    else if (cls == PC_THREAD) v = poly_score_set(P, Q, child, S, k, m, sc);
+    unsigned wm = __ballot_sync(0xffffffffu, cls == PC_WARP);
+    while (wm) {
+        const int src = __ffs(wm) - 1;
+        wm &= wm - 1;
+        const int ks = __shfl_sync(0xffffffffu, k, src), ms = __shfl_sync(0xffffffffu, m, src), cs = __shfl_sync(0xffffffffu, child, src);
+        if (lane == src) { int* ids = W.ids(); for (int a = 0; a < k; ++a) ids[a] = (int)S[a]; }
+        __syncwarp();
+        const double r = poly_score_warp(P, Q, cs, ks, ms, W, lane);
+        if (lane == src) v = r;
+        __syncwarp();
+    }
+    return v;
+}
+
+// K2 for the interaction path: one thread per (child, S), grid-stride over the sets (the warp walks 32 sets at a time)
+__global__ void __launch_bounds__(128) poly_score_kernel(SspsDev P, PolyDev Q, int n_sets, const int* __restrict__ child,
+                                                         const int* __restrict__ offsets, const int* __restrict__ members,
+                                                         const double* __restrict__ lambda, double* __restrict__ arena,
+                                                         double* __restrict__ warp_arena, int mcap_p, double* __restrict__ lml_out,
+                                                         double* __restrict__ lp_out) {
+    const int lane = threadIdx.x & 31;
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+    const PolyScratch sc{arena + gtid, nthreads};
+    const PolyWarpScratch W{warp_arena + (size_t)(gtid >> 5) * poly_warp_scratch_doubles(P.n, mcap_p), P.n, mcap_p};
+    for (int s0 = gtid - lane; s0 < n_sets; s0 += nthreads) {
+        const int s = s0 + lane;
+        const bool live = s < n_sets;
+        const int i = live ? child[s] : 0, k = live ? offsets[s + 1] - offsets[s] : 0;
+        const int* mem = members + (live ? offsets[s] : 0);
+        uint16_t S[SSPS_POLY_KLIST];
+        int m = 0;
+        const bool scored = live && k <= SSPS_POLY_KLIST && poly_class(k, Q.deg, P.n, m) != PC_REFUSE;
+        if (scored) for (int a = 0; a < k; ++a) S[a] = (uint16_t)mem[a];
+        double v = poly_score_any(P, Q, i, S, scored ? k : 0, scored, sc, W, lane);
+        if (live && !scored) {      // saturated sets of any size are closed form; anything else this large is refused by the host
+            v = poly_class(k, Q.deg, P.n, m) == PC_SAT ? poly_lml_saturated(P, Q, i, k) : __longlong_as_double(0x7ff8000000000000LL);
+        }
+        if (live && lml_out) lml_out[s] = v;
+        if (live && lp_out) {
+            const double lam = lambda[s];
+            double somc = 0.0;
+            for (int a = 0; a < k; ++a) somc += P.omc[(size_t)mem[a] + (size_t)P.V * i];
+            lp_out[s] = -lam * somc - prior_normaliser(P, i, lam);
+        }
     }
 }
 
 // ------------------------------------------------------------------------------------------------
 // K3 for the interaction path: the same sweep (lambda move, then add / swap / remove on the sorted
 // parent list, Gen.mh) as mh_sweeps_kernel, one thread per micro-chain, every proposal scored from
-// scratch by poly_score_set, the acceptance test in the reference order with fp64 logarithms.
+// scratch (closed form / THREAD tier by the lane, WARP tier by the whole warp one lane at a time), the
+// acceptance test in the reference order with fp64 logarithms.
 // Chain state uses the degree-1 layout (slots = id | rank << 16); this kernel keeps the list sorted,
 // so rank = position.  Tallies are incremented at every recorded sample (no lazy credit here).
+// A proposal beyond max_indegree, or one of class PC_REFUSE, is rejected and counted (ssps.h: max_indegree).
 // Included after ssps_mh.cuh (StepDraws, sources, select_move, move_ratio, MhParams).
 // ------------------------------------------------------------------------------------------------
 template <class Source>
 __global__ void __launch_bounds__(128) mh_poly_kernel(const __grid_constant__ SspsDev P, const __grid_constant__ PolyDev Q,
                                                       const __grid_constant__ ChainState st, const __grid_constant__ MhParams prm,
-                                                      const __grid_constant__ Source src, double* __restrict__ arena) {
+                                                      const __grid_constant__ Source src, double* __restrict__ arena,
+                                                      double* __restrict__ warp_arena, const int mcap_p) {
     const int lane = threadIdx.x & 31;
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
     const PolyScratch sc{arena + gtid, (int)(gridDim.x * blockDim.x)};
+    const PolyWarpScratch W{warp_arena + (size_t)(gtid >> 5) * poly_warp_scratch_doubles(P.n, mcap_p), P.n, mcap_p};
     const int V = P.V, thin = prm.thinning;
     unsigned long long s_f3 = 0;
     unsigned s_accp = 0, s_accl = 0, s_k = 0, s_prop = 0;
@@ -190,99 +446,113 @@ __global__ void __launch_bounds__(128) mh_poly_kernel(const __grid_constant__ Ss
         if (task >= prm.n_tasks) break;
         const int i = task / prm.n_slabs;
         const int chain = (task % prm.n_slabs) * 32 + lane;
-        if (chain >= st.n_chains) continue;
-        const size_t sidx = (size_t)i * st.nch_pad + chain;
-        const size_t mc = (size_t)chain * V + i;
+        const bool live = chain < st.n_chains;
+        const size_t sidx = (size_t)i * st.nch_pad + (live ? chain : 0);
+        const size_t mc = (size_t)(live ? chain : 0) * V + i;
         uint32_t* cnt_row = st.counts + mc * V;
         uint32_t* pev = prm.pev ? prm.pev + mc * prm.pev_cap : nullptr;
-        int k = st.k[sidx];
-        double lam = st.lambda[sidx];
-        if (k > SSPS_POLY_KMAX || (Q.deg > 0 && poly_width(k, Q.deg) < 0)) continue;    // cannot happen: refused by ssps_init_chains
-        int S[SSPS_POLY_KMAX], T[SSPS_POLY_KMAX];
-        for (int a = 0; a < k; ++a) S[(int)(slot_ref(st, V, i, a, chain) >> 16)] = (int)(slot_ref(st, V, i, a, chain) & 0xffffu);
+        int k = live ? st.k[sidx] : 0;
+        double lam = live ? st.lambda[sidx] : 0.0;
+        uint16_t S[SSPS_POLY_KLIST], T[SSPS_POLY_KLIST];
+        if (live) for (int a = 0; a < k; ++a) { const uint32_t sl = slot_ref(st, V, i, a, chain); S[(int)(sl >> 16)] = (uint16_t)(sl & 0xffffu); }
         const double* __restrict__ omc_i = P.omc + (size_t)V * i;
-        double lml = poly_score_set(P, Q, i, S, k, sc);
+        double lml = poly_score_any(P, Q, i, S, k, live, sc, W, lane);
         double lam_sum = 0.0, lam_sq = 0.0, lam_logged = lam;
         int n_pev = 0, n_lev = 0;
         DrawCarry cy; cy.valid = 0; cy.z = 0.f; cy.w = 0u;
         for (int l = 1; l <= prm.n_local; ++l) {
-            const StepDraws d = src.get(chain, i, (uint64_t)(prm.sweep0 + l), (int64_t)(l - 1), cy);
-            // ---- lambda move (lambda_vec_proposal + Gen.mh), reference order ----
-            const double lam_new = lam + P.sigma * d.z;
-            if (lam_new >= P.lambda_min && lam_new <= P.lambda_max) {
-                double somc = 0.0;
-                for (int a = 0; a < k; ++a) somc += __ldg(omc_i + S[a]);
-                const double nrm = prior_normaliser(P, i, lam), nrm_new = prior_normaliser(P, i, lam_new);
-                const double w = -(lam_new - lam) * somc - (nrm_new - nrm);
-                if (log(d.u_lam) < w) { lam = lam_new; ++s_accl; }
-            }
-            // ---- parent-set move ----
-            int action, a_ord, r_ord;
-            select_move(P, i, k, d, action, a_ord, r_ord);
-            const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
-            int j_add = -1, j_rem = -1, p = k;
-            if (has_add) {          // ith_nonparent: the a-th id not in S
-                int c = 0;
-                for (int b = 0; b < k; ++b) c += (S[b] - b < a_ord) ? 1 : 0;
-                j_add = a_ord - 1 + c;
-            }
-            if (has_rem) { p = r_ord - 1; j_rem = S[p]; }
-            int kn = 0;
-            bool placed = !has_add;
-            for (int b = 0; b < k; ++b) {           // the proposed set, sorted
-                if (b == p) continue;
-                if (!placed && j_add < S[b]) { T[kn++] = j_add; placed = true; }
-                T[kn++] = S[b];
-            }
-            if (!placed) T[kn++] = j_add;
-            ++s_prop; s_k += (unsigned)kn;
-            const int mw = Q.deg > 0 ? poly_width(kn, Q.deg) : 0;
-            if (mw > 0) {       // 3 x (n m (m + 5) + m^3/3 + 2 m^2 + 2 m) flops (deg > 1); the host divides by 3
-                const unsigned long long m_ = (unsigned long long)mw;
-                s_f3 += 3ull * (unsigned long long)P.n * m_ * (m_ + 5ull) + m_ * m_ * m_ + 6ull * m_ * m_ + 6ull * m_;
-            }
-            // a proposal beyond the path's bounds is rejected and counted (ssps.h: max_indegree), the sweep goes on
-            const bool in_range = !(kn > SSPS_POLY_KMAX || kn > prm.kcap || mw < 0);
-            if (!in_range) atomicAdd(prm.stats + ST_KCAP_REJECT, 1ull);
-            double fwd, bwd;
-            move_ratio(P, i, k, action, fwd, bwd);
-            double dprior = 0.0;
-            if (has_add) dprior = -lam * __ldg(omc_i + j_add);
-            if (has_rem) dprior = dprior + lam * __ldg(omc_i + j_rem);
-            const double lml_new = in_range ? poly_score_set(P, Q, i, T, kn, sc) : lml;
-            const double w = dprior + (lml_new - lml);
-            const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
-            const int rel_now = ceil_div_i(l, thin) - 1;
-            if (in_range && log(d.u_acc) < alpha) {
-                ++s_accp;
-                if (pev) {
-                    if (has_rem && n_pev < prm.pev_cap) pev[n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
-                    if (has_add && n_pev < prm.pev_cap) pev[n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
+            StepDraws d;
+            d.z = 0.0; d.u_lam = 0.5; d.u_act = 0.5; d.u_add = 0.5; d.u_rem = 0.5; d.u_acc = 0.5;
+            int action = ACT_ADD, kn = 0, j_add = -1, j_rem = -1;
+            bool in_range = false;
+            if (live) {
+                d = src.get(chain, i, (uint64_t)(prm.sweep0 + l), (int64_t)(l - 1), cy);
+                // ---- lambda move (lambda_vec_proposal + Gen.mh), reference order ----
+                const double lam_new = lam + P.sigma * d.z;
+                if (lam_new >= P.lambda_min && lam_new <= P.lambda_max) {
+                    double somc = 0.0;
+                    for (int a = 0; a < k; ++a) somc += __ldg(omc_i + S[a]);
+                    const double nrm = prior_normaliser(P, i, lam), nrm_new = prior_normaliser(P, i, lam_new);
+                    const double w = -(lam_new - lam) * somc - (nrm_new - nrm);
+                    if (log(d.u_lam) < w) { lam = lam_new; ++s_accl; }
                 }
-                for (int b = 0; b < kn; ++b) S[b] = T[b];
-                k = kn; lml = lml_new;
-            }
-            // ---- thinned recording ----
-            if (l % thin == 0) {
-                for (int b = 0; b < k; ++b) cnt_row[S[b]] += 1u;
-                lam_sum += lam; lam_sq = fma(lam, lam, lam_sq);
-                if (prm.lev_val && lam != lam_logged) {
-                    if (n_lev < prm.lev_cap) {
-                        prm.lev_val[mc * prm.lev_cap + n_lev] = lam;
-                        prm.lev_idx[mc * prm.lev_cap + n_lev] = (uint16_t)(l / thin);
-                        ++n_lev;
+                // ---- parent-set move: the proposed set, sorted ----
+                int a_ord, r_ord;
+                select_move(P, i, k, d, action, a_ord, r_ord);
+                const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
+                int p = k;
+                if (has_add) {          // ith_nonparent: the a-th id not in S
+                    int c = 0;
+                    for (int b = 0; b < k; ++b) c += ((int)S[b] - b < a_ord) ? 1 : 0;
+                    j_add = a_ord - 1 + c;
+                }
+                if (has_rem) { p = r_ord - 1; j_rem = (int)S[p]; }
+                kn = k + (has_add ? 1 : 0) - (has_rem ? 1 : 0);
+                in_range = kn <= prm.kcap && kn <= SSPS_POLY_KLIST;
+                if (in_range) {
+                    int t = 0;
+                    bool placed = !has_add;
+                    for (int b = 0; b < k; ++b) {
+                        if (b == p) continue;
+                        if (!placed && j_add < (int)S[b]) { T[t++] = (uint16_t)j_add; placed = true; }
+                        T[t++] = S[b];
                     }
-                    lam_logged = lam;
+                    if (!placed) T[t++] = (uint16_t)j_add;
+                }
+                ++s_prop; s_k += (unsigned)kn;
+                int mw = 0;
+                const int cls = poly_class(kn, Q.deg, P.n, mw);
+                if (cls == PC_REFUSE) in_range = false;
+                if (in_range && mw > 0) {   // 3 x (n m (m + 5) + m^3/3 + 2 m^2 + 2 m) flops (deg > 1); the host divides by 3
+                    const unsigned long long m_ = (unsigned long long)mw;
+                    s_f3 += 3ull * (unsigned long long)P.n * m_ * (m_ + 5ull) + m_ * m_ * m_ + 6ull * m_ * m_ + 6ull * m_;
+                }
+                if (!in_range) atomicAdd(prm.stats + ST_KCAP_REJECT, 1ull);
+            }
+            const double lml_new = poly_score_any(P, Q, i, T, kn, live && in_range, sc, W, lane);
+            if (live) {
+                const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
+                double fwd, bwd;
+                move_ratio(P, i, k, action, fwd, bwd);
+                double dprior = 0.0;
+                if (has_add) dprior = -lam * __ldg(omc_i + j_add);
+                if (has_rem) dprior = dprior + lam * __ldg(omc_i + j_rem);
+                const double w = dprior + (lml_new - lml);
+                const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
+                const int rel_now = ceil_div_i(l, thin) - 1;
+                if (in_range && log(d.u_acc) < alpha) {
+                    ++s_accp;
+                    if (pev) {
+                        if (has_rem && n_pev < prm.pev_cap) pev[n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
+                        if (has_add && n_pev < prm.pev_cap) pev[n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
+                    }
+                    for (int b = 0; b < kn; ++b) S[b] = T[b];
+                    k = kn; lml = lml_new;
+                }
+                // ---- thinned recording ----
+                if (l % thin == 0) {
+                    for (int b = 0; b < k; ++b) cnt_row[S[b]] += 1u;
+                    lam_sum += lam; lam_sq = fma(lam, lam, lam_sq);
+                    if (prm.lev_val && lam != lam_logged) {
+                        if (n_lev < prm.lev_cap) {
+                            prm.lev_val[mc * prm.lev_cap + n_lev] = lam;
+                            prm.lev_idx[mc * prm.lev_cap + n_lev] = (uint16_t)(l / thin);
+                            ++n_lev;
+                        }
+                        lam_logged = lam;
+                    }
                 }
             }
         }
-        for (int b = 0; b < k; ++b) slot_ref(st, V, i, b, chain) = (uint32_t)S[b] | ((uint32_t)b << 16);
-        st.k[sidx] = k;
-        st.lambda[sidx] = lam;
-        st.lam_sum[mc] += lam_sum;
-        st.lam_sq[mc] += lam_sq;
-        if (prm.pev_n) prm.pev_n[mc] = n_pev;
-        if (prm.lev_n) prm.lev_n[mc] = n_lev;
+        if (live) {
+            for (int b = 0; b < k; ++b) slot_ref(st, V, i, b, chain) = (uint32_t)S[b] | ((uint32_t)b << 16);
+            st.k[sidx] = k;
+            st.lambda[sidx] = lam;
+            st.lam_sum[mc] += lam_sum;
+            st.lam_sq[mc] += lam_sq;
+            if (prm.pev_n) prm.pev_n[mc] = n_pev;
+            if (prm.lev_n) prm.lev_n[mc] = n_lev;
+        }
     }
     unsigned long long v[5] = {s_accp, s_accl, s_k, s_f3, s_prop};
     const int slot[5] = {ST_ACCP, ST_ACCL, ST_SUMK, ST_F3, ST_PROP};

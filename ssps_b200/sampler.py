@@ -333,3 +333,9 @@ class Sampler:
         t = C.c_double(0.0)
         check(self._L.ssps_measure_fp64_peak(self._h, C.byref(t)))
         return t.value
+
+    def measure_gather_peak(self, table_bytes: int):
+        """Useful GB/s of random 8-byte gathers from a table of `table_bytes`: (read-only L1 path, L2 only, shared memory)."""
+        a, b, c = C.c_double(0.0), C.c_double(0.0), C.c_double(0.0)
+        check(self._L.ssps_measure_gather_peak(self._h, int(table_bytes), C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value

@@ -38,3 +38,9 @@ def make_synth(V, T=8, M=4, seed=20200701):
     ds = simulate(V, T, M, seed=seed)
     xm, xp = ds.lagged()
     return ds, xm, xp
+
+
+@pytest.fixture(scope="session")
+def synth_v1000():
+    """V = 1000, T = 100, M = 4 (n = 396): the shape of BASELINE.json's config C5 (and of the V = 1000 replay test)."""
+    return make_synth(1000, T=100, M=4)

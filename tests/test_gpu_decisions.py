@@ -75,11 +75,6 @@ def test_decisions_verified_on_c1(c1):
     _assert_verified(st, "C1 V=46 n=18")
 
 
-@pytest.fixture(scope="module")
-def synth_v1000():
-    return make_synth(1000, T=100, M=4)
-
-
 def _replay_vs_oracle(oracle, ds, xm, xp, n_chains, n_sweeps, seed, thinning=1, large_indeg=15.0):
     from ssps_b200 import Sampler
     V = xm.shape[1]

@@ -485,6 +485,154 @@ def test_l1_interaction_design_vs_qr_oracle(oracle, deg):
     assert n_tight >= 50 and worst <= 1e-10, (n_tight, worst)
 
 
+def _poly_class(k, deg, n):
+    """ssps_poly.cuh: poly_class restated (EMPTY / SAT / THREAD / WARP)."""
+    import math
+    m = sum(math.comb(k, d) for d in range(1, min(deg, k) + 1)) if deg > 0 else 0
+    if m == 0:
+        return "empty", 0
+    if m >= n - 1:
+        return "sat", m
+    return ("thread" if (m <= 48 and k <= 12) else "warp"), m
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("deg", [2, 3, 64])
+def test_l1_interaction_design_all_tiers_incl_width_above_n(oracle, deg):
+    """The three scorer classes of ssps_poly.cuh against the oracle's pivoted-QR least squares on the explicitly built design
+    (construct_B + `\\`, dbn_distributions.jl:179-248): one thread per set (<= 48 columns), the whole warp per set (49 .. n-2
+    columns), and the closed form for designs of n-1 columns or more (also wider than n: Julia's QR takes any width).
+    deg 64 >= |S| is Hill's 'full'.  The closed form is the reference's value whenever its rank-cut QR finds rank n-1; sets
+    where it finds less (numerically collinear product columns) are counted and bounded, not asserted to 1e-10."""
+    from ssps_b200 import Sampler
+    ds, xm, xp = make_synth(30, seed=12, T=31, M=4)       # n = 120 rows
+    n = xm.shape[0]
+    P = oracle.Problem(xm, xp, ds.prior_graph, large_indeg=15.0, lambda_prop_std=3.0, regression_deg=deg)
+    rng = np.random.default_rng(100 + deg)
+    kmax = {2: 20, 3: 11, 64: 9}[deg]
+    sets = [sorted(rng.choice(30, size=int(rng.integers(1, kmax + 1)), replace=False).tolist()) for _ in range(160)]
+    sets.append(list(range(30)))                           # every vertex: far beyond any column limit, closed form
+    ch = rng.integers(0, 30, len(sets))
+    with Sampler(regression_deg=deg, large_indeg=15.0, lambda_prop_std=3.0) as s:
+        s.set_data(xm, xp, ds.prior_graph)
+        lml, _ = s.score(ch, sets, np.full(len(sets), 3.0))
+    seen = {"thread": 0, "warp": 0, "sat": 0}
+    tight = {"thread": 0, "warp": 0, "sat": 0}
+    cut, worst_cut = 0, 0.0
+    for e, S in enumerate(sets):
+        cls, m = _poly_class(len(S), deg, n)
+        seen[cls] += 1
+        assert np.isfinite(lml[e]), (S, cls)
+        if len(S) == 30 and deg == 64:
+            continue                                       # 2^30 columns: the reference cannot build this design either
+        ref, rank = oracle.lml_qr(xm, P.Y[:, ch[e]], S, deg=deg, return_rank=True)
+        err = abs(lml[e] - ref) / abs(ref)
+        if cls == "sat":
+            if rank == n - 1:
+                # exact arithmetic gives the closed form; the QR's min-norm solve of a 255-column design of rank 119 is itself
+                # off by 1e-10..1e-9 relative (ip = y'y - n/(n+1) q cancels (n+1)-fold), measured on the oracle alone
+                assert err <= 1e-8, (S, m, rank, err)
+                tight[cls] += 1
+            else:                                          # the reference's QR cut the rank below n - 1: its projection misses a few directions
+                cut += 1; worst_cut = max(worst_cut, err)
+            continue
+        if rank < m:
+            continue                                       # rank-deficient design: min-norm QR vs column skipping (test_l1_saturated_sets)
+        B = oracle.construct_B(xm, S, deg)
+        cond = np.linalg.cond(B)
+        assert err <= max(1e-10, 1e-14 * cond * cond), (S, cls, m, cond, err)
+        if cond <= 300.0:
+            assert err <= 1e-10, (S, cls, m, cond, err)
+            tight[cls] += 1
+    print("deg %d: classes %s, asserted at 1e-10 %s; saturated sets with a rank cut: %d (worst relative deviation %.2e)" % (deg, seen, tight, cut, worst_cut))
+    assert seen["sat"] >= 10 and seen["thread"] >= 10 and tight["sat"] >= 3
+    if deg != 64:
+        assert seen["warp"] >= 10
+    # where the reference's QR cuts the rank (product columns of a nearly noise-free series are numerically collinear) its
+    # projection misses a few of the n - 1 directions and its lml lies a few per cent below the closed form; those sets carry
+    # -1/2 log(1 + n) per column and are left within a few sweeps of a model-drawn start
+    assert worst_cut <= 0.1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("deg", [2, 3])
+def test_l1_warp_tier_on_a_well_conditioned_design(oracle, deg):
+    """The warp-per-set scorer at the north star's 1e-10: Gaussian data (n = 400 rows), whose product columns are well
+    conditioned, so that the normal-equations error (cond^2 eps) stays below the bar for designs of 49..120 columns."""
+    from ssps_b200 import Sampler
+    rng = np.random.default_rng(77 + deg)
+    n, V = 400, 24
+    xm = rng.standard_normal((n, V)); xp = 0.5 * xm[:, ::-1] + 0.1 * xm[:, :1] * xm[:, 1:2] + rng.standard_normal((n, V))
+    prior = (rng.random((V, V)) < 0.2).astype(float)
+    P = oracle.Problem(xm, xp, prior, large_indeg=15.0, lambda_prop_std=3.0, regression_deg=deg)
+    krange = {2: (10, 15), 3: (7, 9)}[deg]
+    sets = [sorted(rng.choice(V, size=int(rng.integers(krange[0], krange[1] + 1)), replace=False).tolist()) for _ in range(40)]
+    ch = rng.integers(0, V, len(sets))
+    with Sampler(regression_deg=deg, large_indeg=15.0, lambda_prop_std=3.0) as s:
+        s.set_data(xm, xp, prior)
+        lml, _ = s.score(ch, sets, np.full(len(sets), 3.0))
+    worst = 0.0
+    for e, S in enumerate(sets):
+        cls, m = _poly_class(len(S), deg, n)
+        assert cls == "warp" and m > 48
+        ref, rank = oracle.lml_qr(xm, P.Y[:, ch[e]], S, deg=deg, return_rank=True)
+        assert rank == m
+        worst = max(worst, abs(lml[e] - ref) / abs(ref))
+    print("deg %d: %d warp-tier sets of %d..%d columns, worst relative error %.2e" % (deg, len(sets), min(_poly_class(len(S), deg, n)[1] for S in sets), max(_poly_class(len(S), deg, n)[1] for S in sets), worst))
+    assert worst <= 1e-10
+
+
+@pytest.mark.gpu
+def test_l2_replay_interaction_design_warp_tier(oracle):
+    """A replayed stream at deg 2 with n = 120 rows and dense starts (large_indeg 10 at V = 20): the chains walk through all
+    three scorer classes (k <= 9: thread, 10..14: warp, >= 15: saturated); same decisions as the oracle chain with the QR scorer."""
+    from ssps_b200 import Sampler
+    ds, xm, xp = make_synth(20, seed=7, T=31, M=4)
+    n = xm.shape[0]
+    P = oracle.Problem(xm, xp, ds.prior_graph, large_indeg=10.0, lambda_prop_std=3.0, regression_deg=2)
+    n_chains, n_sweeps, V = 6, 40, 20
+    rng = np.random.default_rng(5)
+    draws = rng.random((n_sweeps, n_chains, V, 6))
+    draws[..., 0] = rng.standard_normal((n_sweeps, n_chains, V))
+    seen = {"empty": 0, "thread": 0, "warp": 0, "sat": 0}
+    # dense explicit starts (11..14 parents: 66..105 columns, the warp tier; vertex 0 starts empty, vertex 1 with every vertex)
+    init_sets = [[sorted(rng.choice(V, size=int(rng.integers(11, 15)), replace=False).tolist()) for _ in range(V)] for _ in range(n_chains)]
+    for c in range(n_chains):
+        init_sets[c][0] = []
+        init_sets[c][1] = list(range(V))
+    with Sampler(regression_deg=2, large_indeg=10.0, lambda_prop_std=3.0) as s:
+        s.set_data(xm, xp, ds.prior_graph)
+        lmin, _ = s.derived()
+        init_lam = [[lmin + 0.25 + 0.01 * i for i in range(V)] for _ in range(n_chains)]
+        s.generate(n_chains, seed=1, init_parent_sets=init_sets, init_lambda=init_lam)
+        for c in range(n_chains):
+            for S in s.state(c)[0]:
+                seen[_poly_class(len(S), 2, n)[0]] += 1
+        s.replay(draws)
+        st = s.stats()
+        flips = 0
+        for c in range(n_chains):
+            ch = oracle.Chain(P, scorer=oracle.SCORER_QR)
+            ch.set_state(init_sets[c], init_lam[c])
+            ch.recorder_enable()
+            for t in range(n_sweeps):
+                ch.sweep(draws[t, c])
+                ch.record()
+            sets, lam, lml = s.state(c)
+            for S in sets:
+                seen[_poly_class(len(S), 2, n)[0]] += 1
+            if sets != ch.parent_sets():
+                flips += 1
+                continue
+            assert np.allclose(lam, ch.lambdas(), rtol=0, atol=1e-12)
+            np.testing.assert_allclose(lml, ch.lmls(), rtol=1e-7)    # normal equations vs QR on collinear product columns: cond^2 eps (L1 tests)
+            assert np.array_equal(s.chain_edge_counts()[c], ch.edge_counts())
+        assert st.n_proposals == n_chains * V * n_sweeps
+    print("classes of the start and end states:", seen, "chains with a flipped decision:", flips)
+    assert seen["warp"] > 50 and seen["sat"] > 0
+    assert flips == 0
+
+
 @pytest.mark.gpu
 def test_regression_deg_default_is_the_reference_empty_design(oracle):
     """--regression-deg -1 (the CLI default): construct_B loops over 1:-1, the design is empty and
