@@ -391,20 +391,23 @@ def run_ours(args, rank, world, local_rank):
         e2e_step(1000)
         barrier()
         cold_s = time.perf_counter() - tc
-        for w in range(min(args.warmup, 2)):
+        for w in range(max(args.warmup, 3)):
             e2e_step(1001 + w)
         barrier()
         t0 = time.perf_counter()
         n_e2e = max(10, args.steps) if not args.e2e_steps else args.e2e_steps
+        step_ms = []
         for k in range(n_e2e):
+            ts = time.perf_counter()
             e2e_step(2000 + k)
+            step_ms.append(1e3 * (time.perf_counter() - ts))
         barrier()
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e = {"value": world * C * V * S * n_e2e / float(tt.item()), "unit": UNIT, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "steps": n_e2e,
+               "d2h_bytes_per_step": d2h, "steps": n_e2e, "step_ms": [round(x, 2) for x in step_ms],
                "cold_first_step": {"value": world * C * V * S / cold_s, "seconds": cold_s,
                                    "what": "the same step on an empty block cache (all device memory from cudaMalloc), not in `value`"},
                "what": "per step: ssps_create + set_data(H2D) + init_chains + %d sweeps + psrf + edge_posterior(D2H), wall clock; steady state: "

@@ -62,7 +62,8 @@ enum { ST_ACCP = 0, ST_ACCL = 1, ST_SUMK = 2, ST_F3 = 3, ST_BYTES = 4, ST_KCAP_R
        ST_MISMATCH = 10, ST_BIG_CYCLES = 11, ST_LAM_EXACT = 12, ST_BIG_STEPS = 13, ST_MID_STEPS = 14, ST_MID_CYCLES = 15, ST_PROF = 16,
        ST_DEC_MISMATCH = 24, ST_LAM_DEC_MISMATCH = 25,      // VERIFY: screened decision != reference-order fp64 decision
        ST_MARGIN_USE = 26, ST_LAM_MARGIN_USE = 27,          // VERIFY: max |screening error| / margin as float bits (low word)
-       ST_N = 32 };
+       ST_MID_PROF = 32,                                    // profiling build: MID tier cycles by section (8 slots)
+       ST_N = 48 };
 
 __device__ __forceinline__ float fast_lg2(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float fast_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -707,160 +708,182 @@ __device__ __forceinline__ int small_move(const SspsDev& P, const int child, con
 #undef NL
 
 // ------------------------------------------------------------------------------------------------
-// MID: the parent-set move of a BIG-tier lane whose current set has fewer than SSPS_KM members, done by
-// the lane ITSELF with rolled loops (small code, every such lane of the warp at the same time) on a
-// shared-memory copy F of its factor (a slot of the warp's Stage, filled by the whole warp: the arena
-// is global memory and a dependent chain of L2 round trips per lane cost 58 000 cycles per move).  The
-// warp-cooperative pass below costs tens of thousands of cycles whatever the size and serialises the
-// lanes; sets of 7..12 parents are 80 % of the BIG-tier proposals at the metric point and need a few
-// hundred fma.  Same rows, same operation order, same bits as small_move / big_phase.  The move is
-// applied to F in place (new row a overwrites old row a, whose only reader -- new row a - 1 -- is done);
-// the arena (ids, ranks, factor) is touched only on accept.  F: TRI-packed rows, w behind SSPS_TRI(SSPS_KM).
+// MID: the parent-set move of BIG-tier lanes whose current set has fewer than SSPS_KM members (6 .. 15 parents: 1.1 % of the
+// proposals at the metric point, most of them k = 6 or 7).  TWO such lanes per call, one per HALF-WARP: the 16 lanes of a half
+// copy their subject's factor from its arena block into a slot of the warp's shared-memory Stage and recompute the rows
+// [p, kn) of the proposed set there IN PLACE (new row a overwrites old row a, whose only reader -- new row a - 1 -- is done),
+// row by row, a lane per COLUMN: at step b lane b hands  l_ab = s_b / d_b  to the half by a 16-wide shuffle and every lane
+// c > b subtracts  l_ab l_cb  from its s_c -- a forward substitution, each entry receiving its terms in ascending b
+// through fma: the operation order of small_move / fac_append / the oracle, the same bits.  Entries left of the removed
+// column p are the cached ones.  ids, ranks and the arena are touched only on accept.
+// Round 1 / 2a let every MID lane do its own move serially (mid_move): 13 500 cycles per move measured (300 instructions per
+// recomputed row from ONE lane while 31 wait), a quarter to a third of all task cycles for 1 % of the proposals; a row costs
+// the half-warp  ~50 cycles per column + one 1/sqrt  instead.
+// Slot layout: TRI-packed rows (1/d on the diagonal), w behind SSPS_TRI(SSPS_KM), then ids (words) and ranks (halves).
+// All arguments but the lane state are warp-uniform; every lane of the warp must call.  s0 / s1 = subject lanes of half
+// 0 / 1 (s1 = -1: none).  acc_kn of a subject lane receives  accepted | |S'| << 1.
 // ------------------------------------------------------------------------------------------------
 #ifndef SSPS_KM
 #define SSPS_KM 16
 #endif
-#ifndef SSPS_MID_UNROLL
-#define SSPS_MID_UNROLL 1    // inner loops of mid_move: 1 = smallest code (what a rarely visited path pays for)
-#endif
-#define SSPS_PRAGMA_(x) _Pragma(#x)
-#define SSPS_PRAGMA(x) SSPS_PRAGMA_(x)
-#define SSPS_UNROLL_MID SSPS_PRAGMA(unroll SSPS_MID_UNROLL)
 #define SSPS_MID_SLOT (SSPS_ROWLEN(SSPS_KM) + SSPS_KM)            // doubles: factor, w, then ids (words) and ranks (halves)
-#define SSPS_MID_SLOTS (SSPS_ROWLEN(SSPS_KST) / SSPS_MID_SLOT)
 template <bool VERIFY>
-__device__ __noinline__ int mid_move(const SspsDev& P, const int child, const StepDraws& d, const Move& mv, Lane& L, const SmallAcc& S, const BigRef B,
-                                     double* F, const KCtx& C, const int rel_now, int& kn_out) {
-    const int V = P.V, k = L.k;
-    const unsigned foff = (unsigned)(F - ssps_smem);                        // F is a slot of the warp's shared-memory Stage
+__device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const StepDraws& d, const Move& mv, Lane L, const SmallAcc& S, const KCtx& C,
+                                      const int rel_now, const int s0, const int s1, int* acc_kn) {
+    const int lane = threadIdx.x & 31, half = lane >> 4, hl = lane & 15;
+    const int V = P.V;
+    const int src = half ? s1 : s0;                     // this half's subject lane
+    const bool on = src >= 0;
+    const int srcl = on ? src : s0;
+    const unsigned foff = (unsigned)(C.st_smem.t - ssps_smem) + (unsigned)half * SSPS_MID_SLOT;
 #define FS(e) ssps_smem[foff + (e)]
-    const uint32_t* Fid = (const uint32_t*)(ssps_smem + foff + SSPS_ROWLEN(SSPS_KM));      // id | rel << 16, arrival order (the CURRENT set throughout)
-    const uint16_t* Frk = (const uint16_t*)(Fid + SSPS_KM);                 // sorted ranks
-#define FID(b) ((int)(Fid[b] & 0xffffu))
-    const int action = mv.action, a_ord = mv.a_ord, r_ord = mv.r_ord;
+#define FW(e) FS(SSPS_TRI(SSPS_KM) + (e))
+    uint32_t* const Fid = (uint32_t*)(ssps_smem + foff + SSPS_ROWLEN(SSPS_KM));      // id | rel << 16, arrival order (the CURRENT set until the commit)
+    uint16_t* const Frk = (uint16_t*)(Fid + SSPS_KM);                                 // sorted ranks
+    const double* __restrict__ Ri = P.R + (size_t)V * child;
+    const int k = __shfl_sync(SSPS_FULL, L.k, srcl);
+    const int action = __shfl_sync(SSPS_FULL, mv.action, srcl);
+    const int a_ord = __shfl_sync(SSPS_FULL, mv.a_ord, srcl);
+    const int r_ord = __shfl_sync(SSPS_FULL, mv.r_ord, srcl);
+    const BigRef B = C.big(srcl);
+    if (on) {       // the subject's factor, ids and ranks into the slot
+        for (int e = hl; e < SSPS_TRI(k); e += 16) FS(e) = B.f[e];
+        if (hl < k) { FW(hl) = B.fw()[hl]; Fid[hl] = B.w[hl]; Frk[hl] = B.r[hl]; }
+    }
+    __syncwarp();
     const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
+    const unsigned hshift = 16u * (unsigned)half;
+    const bool mem = on && hl < k;
+    const uint32_t myw = mem ? Fid[hl] : 0u;
+    const int myid = (int)(myw & 0xffffu), myrk = mem ? (int)Frk[hl] : -1;
     int j_add = -1, j_rem = -1, p = k, rp = 1 << 20;
     uint32_t w_rem = 0;
-    if (has_add) {          // ith_nonparent on the sorted list: the a-th id not in S
-        int c = 0;
-        #pragma unroll 1
-        for (int b = 0; b < k; ++b) c += (FID(b) - (int)Frk[b] < a_ord) ? 1 : 0;
-        j_add = a_ord - 1 + c;
-    }
-    if (has_rem) {          // the r-th element of the sorted list
-        rp = r_ord - 1;
-        #pragma unroll 1
-        for (int b = 0; b < k; ++b) if ((int)Frk[b] == rp) p = b;
-        w_rem = Fid[p]; j_rem = (int)(w_rem & 0xffffu);
+    {   // ith_nonparent on the sorted list: the a-th id not in S; the r-th element of the sorted list
+        const unsigned ba = (__ballot_sync(SSPS_FULL, mem && myid - myrk < a_ord) >> hshift) & 0xffffu;
+        const unsigned br = (__ballot_sync(SSPS_FULL, mem && myrk == r_ord - 1) >> hshift) & 0xffffu;
+        if (has_add) j_add = a_ord - 1 + __popc(ba);
+        if (has_rem && br) { rp = r_ord - 1; p = __ffs(br) - 1; w_rem = Fid[p]; j_rem = (int)(w_rem & 0xffffu); }
     }
     const int kr = k - (has_rem ? 1 : 0);
     const int kn = kr + (has_add ? 1 : 0);
-    kn_out = kn;
-    if (kn > C.kcap) { atomicAdd(C.stats + ST_KCAP_REJECT, 1ull); return 0; }
-    const double fwd = mv.fwd, bwd = mv.bwd;
-    const double* __restrict__ omc_i = P.omc + (size_t)V * child;
-    const double* __restrict__ Ri = P.R + (size_t)V * child;
-    double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
-    if (has_add) { omc_add = __ldg(omc_i + j_add); dprior = -L.lam * omc_add; }
-    if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
-
-#define FW(e) FS(SSPS_TRI(SSPS_KM) + (e))
+    const bool work = on && kn <= C.kcap;
+    // q over the unchanged rows
     double q_new = 0.0;
-    #pragma unroll 1
-    for (int m = 0; m < p && m < kr; ++m) q_new = fma(FW(m), FW(m), q_new);
-    // rows [p, kn) of the proposed set: old slots p + 1 .. k - 1 (entries left of column p are the cached ones), then the
-    // arriving parent's row (position kr, nothing cached) -- one loop, one copy of the code
+    if (work) {
 #pragma unroll 1
-    for (int a = p; a < kn; ++a) {
-        const bool arr = a == kr;
-        const int ja = arr ? j_add : FID(a + 1);
+        for (int m = 0; m < p && m < kr; ++m) { const double wm = FW(m); q_new = fma(wm, wm, q_new); }
+    }
+    // rows [p, kn) of the proposed set; the row loop is warp-uniform (shuffles inside), a half works on the rows of its own range
+    const int a_lo = work ? p : (1 << 20), a_hi = work ? kn : 0;
+    const int a_min = min(a_lo, __shfl_xor_sync(SSPS_FULL, a_lo, 16)), a_max = max(a_hi, __shfl_xor_sync(SSPS_FULL, a_hi, 16));
+#pragma unroll 1
+    for (int a = a_min; a < a_max; ++a) {
+        const bool act = a >= a_lo && a < a_hi;
+        const bool arr = a == kr;                               // the arriving parent's row (nothing cached)
         const int c0 = arr ? 0 : p;
-        const double* __restrict__ Ga = P.G + (size_t)ja * V;
-        const double gaa = __ldg(Ga + ja);
-        double d2 = gaa, t = __ldg(Ri + ja);
-        const int olda = SSPS_TRI(a + 1), xa = SSPS_TRI(a);
-SSPS_UNROLL_MID
-        for (int b = 0; b < c0; ++b) { const double l = FS(olda + b); FS(xa + b) = l; d2 = fma(-l, l, d2); t = fma(-l, FW(b), t); }
-SSPS_UNROLL_MID
-        for (int b = c0; b < a; ++b) FS(xa + b) = __ldg(Ga + FID(b + (b >= p ? 1 : 0)));     // the gathers first, back to back: what follows is a dependent chain
-#pragma unroll 1
-        for (int b = c0; b < a; ++b) {
-            const int xb = SSPS_TRI(b);
-            double s = FS(xa + b);
-SSPS_UNROLL_MID
-            for (int m = 0; m < b; ++m) s = fma(-FS(xa + m), FS(xb + m), s);
-            const double l = s * FS(xb + b);
-            FS(xa + b) = l; d2 = fma(-l, l, d2); t = fma(-l, FW(b), t);
+        const int xa = SSPS_TRI(a), olda = SSPS_TRI(a + 1);
+        int ja = 0;
+        double sc = 0.0, gaa = 1.0, t = 0.0;
+        if (act) {
+            ja = arr ? j_add : (int)(Fid[a + 1] & 0xffffu);
+            const double* __restrict__ Ga = P.G + (size_t)ja * V;
+            if (hl >= c0 && hl < a) sc = __ldg(Ga + (int)(Fid[hl + (hl >= p ? 1 : 0)] & 0xffffu));
+            gaa = __ldg(Ga + ja); t = __ldg(Ri + ja);
         }
-        double inv = 0.0, w = 0.0;
-        if (d2 > SSPS_PIVOT_TOL * gaa) { inv = inv_sqrt_ieee(d2); w = t * inv; }
-        else if (d2 != d2 || gaa != gaa) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; }
-        FS(xa + a) = inv; FW(a) = w;
-        q_new = fma(w, w, q_new);
-    }
-    const double ip_new = C.yty - P.shrink * q_new;
-    const float lg_new = fast_lg2((float)ip_new);
-    const bool accept = mh_accept_ool<VERIFY>(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats);
-
-    if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
-        int t = 0;
-        const Scratch xs = C.xs_of(threadIdx.x & 31);
+        double d2 = gaa;
 #pragma unroll 1
-        for (int b = 0; b < k; ++b) if (b != p) xs.T(t++) = (uint16_t)FID(b);
-        if (j_add >= 0) xs.T(t++) = (uint16_t)j_add;
-        const double lml_ref = score_set(P, child, xs, t, nullptr);
-        const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
-        if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
-    }
-    if (!accept) return 0;
-
-    if (has_rem) {
-        const int credit = rel_now - (int)(w_rem >> 16);
-        if (credit > 0) atomicAdd(C.cnt_row + j_rem, (uint32_t)credit);     // RED: the lane owns the counter, nothing waits for the old value
-        if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)j_rem | ((uint32_t)(rel_now + 1) << 16);
-    }
-    if (has_add && C.pev && L.n_pev < C.pev_cap)
-        C.pev[L.n_pev++] = (uint32_t)j_add | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
-    L.somc = (L.somc - omc_rem) + omc_add;
-    L.ip = ip_new; L.lg_ip = lg_new;
-    L.k = kn;
-    if (kn <= SSPS_KS) {    // a removal that brings the set back into the SMALL tier (no arrival: kn = kr)
-        #pragma unroll 1
-        for (int a = 0; a < kn; ++a) {
-            const int oa = a + (a >= p ? 1 : 0);
-            int r = (int)Frk[oa];
-            r -= (r > rp) ? 1 : 0;
-            S.W(a) = Fid[oa]; S.set_rank(a, r);
-            const int row = SSPS_TRI(a);
-            #pragma unroll 1
-            for (int m = 0; m <= a; ++m) S.d[(SSPS_TRI(a) + m) * SSPS_BLOCK] = FS(row + m);
-            S.Wv(a) = FW(a);
+        for (int b = 0; b < a; ++b) {
+            const double invb = FS(SSPS_TRI(b) + b), wb = FW(b);
+            const double lsh = __shfl_sync(SSPS_FULL, sc * invb, b, 16);
+            if (act) {
+                const double l = (b < c0) ? FS(olda + b) : lsh;
+                d2 = fma(-l, l, d2); t = fma(-l, wb, t);
+                if (hl > b && hl >= c0 && hl < a) sc = fma(-l, FS(SSPS_TRI(hl) + b), sc);
+                if (hl == b) FS(xa + b) = l;
+            }
         }
-        L.mode = MODE_SMALL;
-        return 1;
+        if (act) {
+            double inv = 0.0, w = 0.0;
+            if (d2 > SSPS_PIVOT_TOL * gaa) { inv = inv_sqrt_ieee(d2); w = t * inv; }
+            else if (d2 != d2 || gaa != gaa) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; }
+            q_new = fma(w, w, q_new);
+            if (hl == 0) { FS(xa + a) = inv; FW(a) = w; }
+        }
+        __syncwarp();
     }
-    int rj = 0;
-    #pragma unroll 1
-    for (int a = 0; a < kr; ++a) {      // id list: close the gap at p, shift the sorted ranks
-        const int oa = a + (a >= p ? 1 : 0);
-        const uint32_t w = Fid[oa];
-        int r = (int)Frk[oa];
-        r -= (r > rp) ? 1 : 0;
-        if (has_add) { if ((int)(w & 0xffffu) < j_add) ++rj; else ++r; }
-        B.w[a] = w; B.r[a] = (uint16_t)r;
+    // ---- the subject lanes: acceptance (they may sit in either half: the move's numbers come from lane 0 of the half that did the work) ----
+    const int wh = (lane == s1) ? 16 : 0;
+    const double q_s = __shfl_sync(SSPS_FULL, q_new, wh);
+    const int jadd_s = __shfl_sync(SSPS_FULL, j_add, wh), jrem_s = __shfl_sync(SSPS_FULL, j_rem, wh);
+    const int kn_s = __shfl_sync(SSPS_FULL, kn, wh);
+    const uint32_t wrem_s = __shfl_sync(SSPS_FULL, w_rem, wh);
+    const int work_s = __shfl_sync(SSPS_FULL, work ? 1 : 0, wh);
+    int acc = 0;
+    if (lane == s0 || lane == s1) {
+        const int ks = L.k, act_s = mv.action;
+        const bool add_s = act_s != ACT_REM, rem_s = act_s != ACT_ADD;
+        if (!work_s) { atomicAdd(C.stats + ST_KCAP_REJECT, 1ull); *acc_kn = kn_s << 1; }
+        else {
+            const double* __restrict__ omc_i = P.omc + (size_t)V * child;
+            double omc_add = 0.0, omc_rem = 0.0, dprior = 0.0;
+            if (add_s) { omc_add = __ldg(omc_i + jadd_s); dprior = -L.lam * omc_add; }
+            if (rem_s) { omc_rem = __ldg(omc_i + jrem_s); dprior = dprior + L.lam * omc_rem; }
+            const double ip_new = C.yty - P.shrink * q_s;
+            const float lg_new = fast_lg2((float)ip_new);
+            acc = mh_accept_ool<VERIFY>(P, act_s, ks, kn_s, dprior, mv.fwd, mv.bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats) ? 1 : 0;
+            if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
+                const uint32_t* ids_s = (const uint32_t*)(ssps_smem + (unsigned)(C.st_smem.t - ssps_smem) + (unsigned)(wh >> 4) * SSPS_MID_SLOT + SSPS_ROWLEN(SSPS_KM));
+                int tt = 0;
+                const Scratch xs = C.xs_of(lane);
+#pragma unroll 1
+                for (int b = 0; b < ks; ++b) if (!rem_s || (int)(ids_s[b] & 0xffffu) != jrem_s) xs.T(tt++) = (uint16_t)(ids_s[b] & 0xffffu);
+                if (add_s) xs.T(tt++) = (uint16_t)jadd_s;
+                const double lml_ref = score_set(P, child, xs, tt, nullptr);
+                const double lml_new = -0.5 * (double)kn_s * P.log1pn - 0.5 * P.dn * log(ip_new);
+                if (!(lml_ref == lml_new || (lml_ref != lml_ref && lml_new != lml_new))) atomicAdd(C.stats + ST_MISMATCH, 1ull);
+            }
+            if (acc) {
+                if (rem_s) {
+                    const int credit = rel_now - (int)(wrem_s >> 16);
+                    if (credit > 0) atomicAdd(C.cnt_row + jrem_s, (uint32_t)credit);     // RED: the lane owns the counter, nothing waits for the old value
+                    if (C.pev && L.n_pev < C.pev_cap) C.pev[L.n_pev++] = (uint32_t)jrem_s | ((uint32_t)(rel_now + 1) << 16);
+                }
+                if (add_s && C.pev && L.n_pev < C.pev_cap)
+                    C.pev[L.n_pev++] = (uint32_t)jadd_s | ((uint32_t)(rel_now + 1) << 16) | 0x80000000u;
+                L.somc = (L.somc - omc_rem) + omc_add;
+                L.ip = ip_new; L.lg_ip = lg_new;
+                L.k = kn_s;
+                if (kn_s <= SSPS_KS) L.mode = MODE_SMALL;
+            }
+            *acc_kn = acc | (kn_s << 1);
+        }
     }
-    if (has_add) { B.w[kr] = (uint32_t)j_add | ((uint32_t)rel_now << 16); B.r[kr] = (uint16_t)rj; }
-    double* __restrict__ fw = B.fw();
-    #pragma unroll 1
-    for (int a = p; a < kn; ++a) {      // recomputed rows over the arena rows (proposed set's coordinates)
-        const int xa = SSPS_TRI(a);
-        double* __restrict__ dst = B.f + SSPS_TRI(a);
-        #pragma unroll 1
-        for (int m = 0; m <= a; ++m) dst[m] = FS(xa + m);
-        fw[a] = FW(a);
+    // ---- commit (the half that did the work): ids with the gap at p closed and the sorted ranks shifted, rows [p, kn) ----
+    const int acc_h = __shfl_sync(SSPS_FULL, acc, srcl);
+    if (on && acc_h) {
+        uint32_t wv = 0; int rv = 0;
+        if (hl < kr) {
+            const int oa = hl + (hl >= p ? 1 : 0);
+            wv = Fid[oa]; rv = (int)Frk[oa];
+            rv -= (rv > rp) ? 1 : 0;
+        }
+        const unsigned lt = (__ballot_sync(0xffffu << hshift, hl < kr && (int)(wv & 0xffffu) < j_add) >> hshift) & 0xffffu;
+        if (has_add) { if (hl < kr && !((int)(wv & 0xffffu) < j_add)) ++rv; }
+        if (hl == kr && has_add) { wv = (uint32_t)j_add | ((uint32_t)rel_now << 16); rv = __popc(lt); }
+        if (kn <= SSPS_KS) {        // a removal that brings the set back into the SMALL tier
+            const SmallAcc Ss = S.of_lane(src - lane);
+            for (int e = hl; e < SSPS_TRI(kn); e += 16) Ss.d[e * SSPS_BLOCK] = FS(e);
+            if (hl < kn) { Ss.Wv(hl) = FW(hl); Ss.W(hl) = wv; Ss.set_rank(hl, rv); }
+        } else {
+            if (hl < kn) { B.w[hl] = wv; B.r[hl] = (uint16_t)rv; }
+            double* __restrict__ fw = B.fw();
+            for (int e = SSPS_TRI(p) + hl; e < SSPS_TRI(kn); e += 16) B.f[e] = FS(e);
+            if (hl >= p && hl < kn) fw[hl] = FW(hl);
+        }
     }
-    return 1;
-#undef FID
+    __syncwarp();
+    if (lane == 0) atomicAdd(C.stats + ST_MID_STEPS, (unsigned long long)(1 + (s1 >= 0 ? 1 : 0)));
+    return L;
 #undef FS
 #undef FW
 }
@@ -1519,36 +1542,20 @@ __global__ void __launch_bounds__(SSPS_BLOCK, SSPS_MIN_CTAS) mh_sweeps_kernel(co
                 acc_kn = acc | (kn << 1);
             }
             unsigned midm = __ballot_sync(SSPS_FULL, is_mid);
-            while (midm) {      // rounds of SSPS_MID_SLOTS lanes: the warp copies their factors into Stage slots, each lane moves its own
-                const int my_slot = __popc(midm & ((1u << lane) - 1u));
-                const bool mine = is_mid && ((midm >> lane) & 1u) && my_slot < SSPS_MID_SLOTS;
-                const unsigned round = __ballot_sync(SSPS_FULL, mine);
-                if (lane == 0) atomicAdd(prm.stats + ST_MID_STEPS, (unsigned long long)__popc(round));
-                unsigned rm = round;
-                double* Fs = C.st_smem.t;
-                while (rm) {
-                    const int src_l = __ffs(rm) - 1;
-                    rm &= rm - 1;
-                    const int ks = __shfl_sync(SSPS_FULL, L.k, src_l);
-                    const BigRef Bs = C.big(src_l);
-                    for (int e = lane; e < SSPS_TRI(ks); e += 32) Fs[e] = Bs.f[e];
-                    if (lane < ks) {
-                        Fs[SSPS_TRI(SSPS_KM) + lane] = Bs.fw()[lane];
-                        uint32_t* const Fid = (uint32_t*)(Fs + SSPS_ROWLEN(SSPS_KM));
-                        Fid[lane] = Bs.w[lane];
-                        ((uint16_t*)(Fid + SSPS_KM))[lane] = Bs.r[lane];
-                    }
-                    Fs += SSPS_MID_SLOT;
-                }
-                __syncwarp();
-                if (mine) {
-                    int kn = 0;
-                    const int acc = mid_move<VERIFY>(P, i, d, mv, L, S, C.big(lane), C.st_smem.t + my_slot * SSPS_MID_SLOT, C, rel_now, kn);
-                    acc_kn = acc | (kn << 1);
-                }
-                __syncwarp();
-                midm &= ~round;
+#ifdef SSPS_PROFILE_BIG
+            const long long t_mid_ = midm ? clock64() : 0;
+            const unsigned midm0_ = midm;
+#endif
+            while (midm) {      // two MID lanes per pass, one per half-warp
+                const int s0 = __ffs(midm) - 1;
+                midm &= midm - 1;
+                const int s1 = midm ? __ffs(midm) - 1 : -1;
+                midm &= midm - 1;                   // (0 & anything = 0)
+                L = mid_pair<VERIFY>(P, i, d, mv, L, S, C, rel_now, s0, s1, &acc_kn);
             }
+#ifdef SSPS_PROFILE_BIG
+            if (midm0_ && lane == 0) { atomicAdd(prm.stats + ST_MID_CYCLES, (unsigned long long)(clock64() - t_mid_)); atomicAdd(prm.stats + ST_MID_PROF + 2, (unsigned long long)((__popc(midm0_) + 1) / 2)); }
+#endif
             if (bigm) L = big_phase<VERIFY>(P, i, d, mv, L, S, C, rel_now, bigm, 0u, &acc_kn);
             const bool record = ++phase == thin;
             if (record) { phase = 0; ++rec_done; }

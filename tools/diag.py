@@ -28,7 +28,8 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
               (st.big_cycles - prev.big_cycles) / max(float(s.vertex_cost()[0].sum()) * 4, 1.0)))
         prev = st
         r = s.raw_stats(32)
-        print("      mid: %d lane-steps (%.2e per proposal), (cumulative)" % (r[14], r[14] / max(st.n_proposals, 1)))
+        print("      mid: %d lane-steps (%.2e per proposal), %.0f cycles per lane-step, %.3f of all task cycles (cumulative; cycles only in the profiling build)"
+              % (r[14], r[14] / max(st.n_proposals, 1), r[15] / max(r[14], 1), r[15] / max(float(s.vertex_cost()[0].sum()) * (rep + 1), 1.0)))
     cost, mk, sp = s.vertex_cost()
     n_slabs = (C + 31) // 32
     task = cost / (n_slabs * sp)
@@ -40,7 +41,9 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
     if os.environ.get('DIAG_KHIST'):
         print("khist:", s.khist(40).tolist())
     if os.environ.get('DIAG_PROF'):
-        r = s.raw_stats(32)
+        r = s.raw_stats(48)
+        if r[34]:
+            print("MID: %d passes (two lanes each at most), %.0f cycles per pass, %.0f per lane-step" % (r[34], r[15] / r[34], r[15] / max(r[14], 1)))
         names = ["select+bcast", "stage_load", "scans", "remove (+q prefix)", "append", "accept (src lane)", "commit", "promote+tail"]
         tot = float(r[16:24].sum()) or 1.0
         print("BIG phase cycles by section (profiling build): " + ", ".join("%s %.1f%%" % (n, 100 * r[16 + e] / tot) for e, n in enumerate(names)),

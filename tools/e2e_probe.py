@@ -4,7 +4,7 @@ import numpy as np
 from bench import make_workload
 from ssps_b200 import Sampler
 ds, xm, xp = make_workload(100, 8, 4)
-for rep in range(6):
+for rep in range(int(sys.argv[1]) if len(sys.argv) > 1 else 6):
     t0 = time.perf_counter()
     s = Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=100)
     s.set_data(xm, xp, ds.prior_graph)
