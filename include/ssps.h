@@ -51,7 +51,7 @@
 extern "C" {
 #endif
 
-#define SSPS_ABI_VERSION 3
+#define SSPS_ABI_VERSION 4
 
 typedef enum {
     SSPS_OK = 0,
@@ -70,9 +70,11 @@ typedef struct {
     int32_t struct_size;      /* = sizeof(ssps_config) */
     int32_t device;           /* CUDA ordinal; -1 = current device */
     int32_t regression_deg;   /* --regression-deg (SSPS.jl:75-78).  1: the tabulated-Gram path.  >= 2: interaction columns
-                                 (construct_B), every proposal scored from scratch, sets limited to 12 parents / 48
-                                 design columns.  <= 0 (the reference CLI's default -1): the reference builds an EMPTY
-                                 design -- flat likelihood -- reproduced as is (quirk Q2) */
+                                 (construct_B), every proposal scored from scratch: one thread per set up to 48 design columns,
+                                 the whole warp per set up to n - 2 columns, closed form from n - 1 columns on (any number of
+                                 parents); any degree >= max_indegree is Hill's "full" (all non-empty product subsets).
+                                 <= 0 (the reference CLI's default -1): the reference builds an EMPTY design -- flat
+                                 likelihood -- reproduced as is (quirk Q2) */
     int32_t max_indegree;     /* bound on |S| (0 = min(V, 128), the most the factor arena supports).  A proposal that would
                                  grow a set beyond the bound is REJECTED (counted in n_indegree_rejects): the chain samples
                                  the posterior truncated at |S| <= max_indegree, never an invalid run.  The reference has
@@ -93,7 +95,10 @@ typedef struct {
                                  min_burnin * samples are recycled first when the snapshot pool is full */
     int32_t snapshot_slots;   /* size of the tally-snapshot pool, allocated ONCE by ssps_init_chains (0 = 32, clamped to
                                  a quarter of the free device memory, at least 4); ssps_run never allocates */
-    int32_t reserved0;
+    int32_t proposal;         /* --proposal (SSPS.jl:87-88): 0 = "sparse", the parent-set proposal (smart_proposal, the default and what
+                                 --multithread forces); 1 = "uniform", the deprecated uniform graph proposal (uniform_update_loop:
+                                 add / remove a uniformly drawn pair or reverse an unpaired edge) -- one thread per chain, every
+                                 changed set scored from scratch; regression_deg <= 1 only */
 } ssps_config;
 
 typedef struct {

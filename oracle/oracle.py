@@ -19,6 +19,7 @@ SCORER_CHOL = 0
 SCORER_QR = 1
 FLAG_LML_CACHE = 1
 FLAG_STALE_PRIOR = 2
+FLAG_UNIFORM = 4
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)

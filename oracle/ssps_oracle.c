@@ -844,6 +844,126 @@ static void chain_step(orc_chain* C, int i, const double d[6], int* acc_out) {
     if (acc_out) { acc_out[0] = acc_l; acc_out[1] = acc_p; acc_out[2] = action; }
 }
 
+/* ------------------------------------------------------------------------------------------
+ * The deprecated uniform graph proposal (--proposal uniform, SSPS.jl:87-88,173-175):
+ *   uniform_update_loop   state_updates.jl:98-112   for i = 1..V: lambda move of vertex i, then ONE uniform graph move
+ *   unpaired_edges        dbn_proposals.jl:142-155  edges (p -> child), p != child, whose reverse is not an edge,
+ *                                                   sorted as (p, child) tuples
+ *   uniform_proposal      dbn_proposals.jl:161-179  idx ~ uniform_discrete(1, V^2 + |ue|); idx <= V^2: the pair
+ *                                                   (u, v) = (div(idx-1, V), (idx-1) % V), REMOVE if u is a parent of v
+ *                                                   else ADD; above: REVERSE the unpaired edge ue[idx - V^2]
+ *   uniform_involution    dbn_proposals.jl:184-230  backward choice = the same cell (add <-> remove) or the position of the
+ *                                                   reversed edge in the new list; Gen.update weight = change of
+ *                                                   (log prior + lml) of the one or two vertices whose parent set changed
+ * Gen.mh accepts iff log(u) < weight + log q(backward) - log q(forward) = weight + log(bound) - log(bound'), bound' =
+ * V^2 + |ue'| of the proposed graph (add / remove change |ue| by +-1, a self-edge and a reversal leave it).
+ * Draw convention (shared with the device): d[2] picks idx = 1 + floor(d[2] bound), d[5] is the acceptance uniform;
+ * d[3], d[4] are not used.  Parent lists: S sorted, A in arrival order (add appends, remove deletes in place).
+ * ---------------------------------------------------------------------------------------- */
+static int set_insert_sorted(int* S, int k, int x) { int a = k; while (a > 0 && S[a - 1] > x) { S[a] = S[a - 1]; --a; } S[a] = x; return k + 1; }
+static int set_erase(int* S, int k, int x) { int t = 0; for (int a = 0; a < k; ++a) if (S[a] != x) S[t++] = S[a]; return t; }
+
+static int64_t count_unpaired(const orc_chain* C) {
+    const int V = C->P->V;
+    int64_t n = 0;
+    for (int c = 0; c < V; ++c)
+        for (int a = 0; a < C->k[c]; ++a) {
+            const int p = C->S[(size_t)c * V + a];
+            if (p != c && !in_sorted(C->S + (size_t)p * V, C->k[p], c)) ++n;
+        }
+    return n;
+}
+/* the r-th (0-based) unpaired edge in (p, child) order */
+static void nth_unpaired(const orc_chain* C, int64_t r, int* p_out, int* c_out) {
+    const int V = C->P->V;
+    for (int p = 0; p < V; ++p)
+        for (int c = 0; c < V; ++c)
+            if (p != c && in_sorted(C->S + (size_t)c * V, C->k[c], p) && !in_sorted(C->S + (size_t)p * V, C->k[p], c)) {
+                if (r == 0) { *p_out = p; *c_out = c; return; }
+                --r;
+            }
+    *p_out = -1; *c_out = -1;
+}
+
+/* lml and prior change of vertex v when parent u is added (add = 1) or removed; the proposed lists go to T / TA */
+static double uniform_delta(orc_chain* C, int v, int u, int add, int* T, int* TA, int* kn_out, double* lml_new_out) {
+    const orc_problem* P = C->P;
+    const int V = P->V, k = C->k[v];
+    const int* S = C->S + (size_t)v * V; const int* A = C->A + (size_t)v * V;
+    memcpy(T, S, sizeof(int) * (size_t)k); memcpy(TA, A, sizeof(int) * (size_t)k);
+    int kn;
+    if (add) { kn = set_insert_sorted(T, k, u); TA[k] = u; }
+    else { kn = set_erase(T, k, u); set_erase(TA, k, u); }
+    const double lml_new = chain_lml(C, v, T, TA, kn);
+    const double lam = C->lambda[v], omc = P->omc[(size_t)u + (size_t)V * v];
+    const double dprior = add ? -lam * omc : lam * omc;
+    *kn_out = kn; *lml_new_out = lml_new;
+    return dprior + (lml_new - C->lml[v]);
+}
+static void uniform_commit(orc_chain* C, int v, const int* T, const int* TA, int kn, double lml_new) {
+    const int V = C->P->V;
+    memcpy(C->S + (size_t)v * V, T, sizeof(int) * (size_t)kn);
+    memcpy(C->A + (size_t)v * V, TA, sizeof(int) * (size_t)kn);
+    C->k[v] = kn; C->lml[v] = lml_new;
+    C->somc[v] = sum_omc(C->P, v, C->S + (size_t)v * V, kn);
+    C->lp[v] = chain_logprior_full(C, v, C->S + (size_t)v * V, kn, C->lambda[v]);
+}
+
+static void chain_step_uniform(orc_chain* C, int i, const double d[6], int* acc_out) {
+    const orc_problem* P = C->P;
+    const int V = P->V;
+    const double z = d[0], u_lam = d[1], u_idx = d[2], u_acc = d[5];
+    int acc_l = 0, acc_p = 0, action = 0;
+    /* lambda move of vertex i (lambda_vec_proposal + Gen.mh), exact prior */
+    {
+        double lam = C->lambda[i];
+        const double lam_new = lam + P->lambda_prop_std * z;
+        if (lam_new >= P->lambda_min && lam_new <= P->lambda_max) {
+            const double nrm_new = normaliser(P, i, lam_new);
+            const double w = -(lam_new - lam) * C->somc[i] - (nrm_new - C->nrm[i]);
+            if (log(u_lam) < w) { lam = lam_new; C->nrm[i] = nrm_new; acc_l = 1; }
+        }
+        C->lambda[i] = lam;
+        C->lp[i] = chain_logprior_full(C, i, C->S + (size_t)i * V, C->k[i], lam);
+    }
+    /* the graph move */
+    const int64_t n_ue = count_unpaired(C);
+    const int64_t vv = (int64_t)V * V, bound = vv + n_ue;
+    int64_t idx = 1 + (int64_t)floor(u_idx * (double)bound); if (idx > bound) idx = bound;
+    int* T1 = (int*)malloc(sizeof(int) * 4 * ((size_t)V + 1));
+    int* TA1 = T1 + V + 1; int* T2 = TA1 + V + 1; int* TA2 = T2 + V + 1;
+    ++C->n_prop;
+    if (idx <= vv) {
+        const int u = (int)((idx - 1) / V), v = (int)((idx - 1) % V);
+        const int is_parent = in_sorted(C->S + (size_t)v * V, C->k[v], u);
+        const int rev = in_sorted(C->S + (size_t)u * V, C->k[u], v);       /* is v -> u an edge? */
+        int kn; double lml_new;
+        action = is_parent ? ORC_ACT_REM : ORC_ACT_ADD;
+        const double w = uniform_delta(C, v, u, !is_parent, T1, TA1, &kn, &lml_new);
+        int64_t n_ue_new = n_ue;
+        if (u != v) n_ue_new += is_parent ? (rev ? 1 : -1) : (rev ? -1 : 1);
+        const double alpha = w + (log((double)bound) - log((double)(vv + n_ue_new)));
+        if (kn < C->khist_len) ++C->khist[kn];
+        if (log(u_acc) < alpha) { acc_p = 1; ++C->n_acc; uniform_commit(C, v, T1, TA1, kn, lml_new); }
+    } else {
+        int u, v;
+        nth_unpaired(C, idx - vv - 1, &u, &v);         /* edge u -> v becomes v -> u */
+        int kn1, kn2; double lml1, lml2;
+        action = ORC_ACT_SWAP;
+        const double w1 = uniform_delta(C, v, u, 0, T1, TA1, &kn1, &lml1);
+        const double w2 = uniform_delta(C, u, v, 1, T2, TA2, &kn2, &lml2);
+        const double alpha = w1 + w2;                  /* |ue| unchanged: the proposal ratio is 1 */
+        if (kn2 < C->khist_len) ++C->khist[kn2];
+        if (log(u_acc) < alpha) {
+            acc_p = 1; ++C->n_acc;
+            uniform_commit(C, v, T1, TA1, kn1, lml1);
+            uniform_commit(C, u, T2, TA2, kn2, lml2);
+        }
+    }
+    free(T1);
+    if (acc_out) { acc_out[0] = acc_l; acc_out[1] = acc_p; acc_out[2] = action; }
+}
+
 void orc_chain_sweep(orc_chain* C, const double* draws, int* acc_out) {
     int V = C->P->V;
     ++C->sweeps;
@@ -851,7 +971,8 @@ void orc_chain_sweep(orc_chain* C, const double* draws, int* acc_out) {
         double d[6];
         if (draws) memcpy(d, draws + (size_t)i * 6, sizeof(d));
         else orc_step_draws(C->seed, C->chain_id, (uint32_t)i, (uint64_t)C->sweeps, d);
-        chain_step(C, i, d, acc_out ? acc_out + (size_t)i * 3 : NULL);
+        if (C->flags & ORC_FLAG_UNIFORM) chain_step_uniform(C, i, d, acc_out ? acc_out + (size_t)i * 3 : NULL);
+        else chain_step(C, i, d, acc_out ? acc_out + (size_t)i * 3 : NULL);
     }
 }
 

@@ -45,7 +45,8 @@ enum { ORC_SCORER_CHOL = 0,   /* Gram-Cholesky, same arithmetic order as the CUD
 
 /* chain mode flags */
 enum { ORC_FLAG_LML_CACHE   = 1,  /* memoise lml on [i;S] like lml_cache (dbn_distributions.jl:161,255-264) */
-       ORC_FLAG_STALE_PRIOR = 2   /* emulate the lambda-blind prior_cache (quirk Q1, dbn_distributions.jl:102) */ };
+       ORC_FLAG_STALE_PRIOR = 2,  /* emulate the lambda-blind prior_cache (quirk Q1, dbn_distributions.jl:102) */
+       ORC_FLAG_UNIFORM     = 4   /* the deprecated uniform graph proposal (uniform_update_loop, state_updates.jl:98-112) */ };
 
 enum { ORC_ACT_ADD = 1, ORC_ACT_SWAP = 2, ORC_ACT_REM = 3 };
 

@@ -11,7 +11,7 @@ import os
 from . import _build
 
 OK = 0
-ABI_VERSION = 3
+ABI_VERSION = 4
 ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NOMEM, ERR_INDEGREE, ERR_UNAVAILABLE = -1, -2, -3, -4, -5, -6
 
 _dp = C.POINTER(C.c_double)
@@ -28,7 +28,7 @@ class Config(C.Structure):
         ("max_indegree", C.c_int32), ("large_indeg", C.c_double), ("lambda_max", C.c_double),
         ("lambda_prop_std", C.c_double), ("psrf_grid", C.c_int32), ("record_changepoints", C.c_int32),
         ("collect_khist", C.c_int32), ("verify", C.c_int32),
-        ("min_burnin", C.c_double), ("snapshot_slots", C.c_int32), ("reserved0", C.c_int32),
+        ("min_burnin", C.c_double), ("snapshot_slots", C.c_int32), ("proposal", C.c_int32),
     ]
 
 

@@ -14,6 +14,7 @@
 #include "ssps_kernels.cuh"
 #include "ssps_mh.cuh"
 #include "ssps_poly.cuh"
+#include "ssps_uniform.cuh"
 #include "ssps_neff.cuh"
 
 #include <algorithm>
@@ -206,6 +207,9 @@ struct ssps_handle {
     SspsDev dev{};
     PolyDev poly{};                 // regression_deg != 1: interaction-column path (csrc/ssps_poly.cuh)
     bool is_poly = false;
+    bool is_uniform = false;        // cfg.proposal == 1: the deprecated uniform graph proposal (csrc/ssps_uniform.cuh)
+    DevBuf<uint32_t> u_par, u_chi;
+    DevBuf<double> u_lml, u_lamlog;
     DevBuf<double> poly_arena, poly_warena;
     int poly_mcap_p = 0;            // WARP tier column capacity (0: tier not needed)
     int poly_grid = 0;
@@ -434,6 +438,9 @@ int ssps_create(const ssps_config* cfg, ssps_handle** out) {
     if (!h) return fail(SSPS_ERR_NOMEM, "out of host memory");
     h->cfg = *cfg;
     h->is_poly = cfg->regression_deg >= 2;
+    h->is_uniform = cfg->proposal == 1;
+    if (cfg->proposal != 0 && cfg->proposal != 1) { delete h; return fail(SSPS_ERR_INVALID, "proposal=%d: 0 (sparse) or 1 (uniform)", cfg->proposal); }
+    if (h->is_uniform && h->is_poly) { delete h; return fail(SSPS_ERR_UNSUPPORTED, "proposal uniform is implemented for regression_deg <= 1 only"); }
     h->device = dev;
     cudaError_t e = cudaSetDevice(dev);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, dev);
@@ -716,8 +723,14 @@ int alloc_chains(ssps_handle* h, int n_chains) {
     CK(h->scr_d.alloc(nthreads / 32 * SSPS_ROWLEN(kc))); CK(h->scr_w.alloc(nthreads / 32 * kc)); CK(h->scr_r.alloc(nthreads / 32 * kc));
     CK(h->big_w.alloc(nthreads * kc));
     CK(h->big_r.alloc(nthreads * kc));
-    CK(h->x_d.alloc(h->cfg.verify ? nthreads * (SSPS_TRI(kc) + kc) : 1));
-    CK(h->x_t.alloc(nthreads * 2 * kc));
+    const size_t xthreads = h->is_uniform ? std::max(nthreads, (size_t)h->nch_pad) : nthreads;
+    CK(h->x_d.alloc(h->is_uniform ? (size_t)h->nch_pad * (SSPS_TRI(kc) + kc) : (h->cfg.verify ? nthreads * (SSPS_TRI(kc) + kc) : 1)));
+    CK(h->x_t.alloc(xthreads * 2 * kc));
+    if (h->is_uniform) {
+        const size_t W = ((size_t)V + 31) / 32;
+        CK(h->u_par.alloc((size_t)V * W * h->nch_pad)); CK(h->u_chi.alloc((size_t)V * W * h->nch_pad));
+        CK(h->u_lml.alloc((size_t)V * h->nch_pad)); CK(h->u_lamlog.alloc((size_t)V * h->nch_pad));
+    }
     CK(h->task_counter.alloc(1));
     CK(h->order.alloc(V)); CK(h->vcost.alloc(V));
     CK(h->task_start.alloc((size_t)V + 1)); CK(h->task_split.alloc(V)); CK(h->task_est.alloc(2 * (size_t)V));
@@ -981,7 +994,7 @@ int run_launch(ssps_handle* h, RunCtx& cx) {
     if (h->snap_grid > 0) rec = std::min(rec, h->snap_grid - h->samples_recorded % h->snap_grid);
     // no measured task costs yet: a short calibration launch, so that the scheduler can split the heavy vertices for the rest
     // of the batch (the first 100-sweep launch of a fresh handle ran 25 % longer than the later ones)
-    if (!h->have_cost && !cx.replay && rec > 24) rec = 8;
+    if (!h->have_cost && !cx.replay && rec > 24 && !h->is_uniform && !h->is_poly) rec = 8;
     const int n_local = (int)(rec * thinning);
     MhParams prm{};
     prm.sweep0 = h->sweeps_done; prm.n_local = n_local; prm.thinning = thinning;
@@ -1017,7 +1030,18 @@ int run_launch(ssps_handle* h, RunCtx& cx) {
     }
     CK(cudaEventRecord(h->ev_pool[cx.ev_used].first, h->stream));
     const double* rp = cx.replay ? cx.replay_dev.p + (size_t)cx.done * C * V * 6 : nullptr;
-    if (h->is_poly) {
+    if (h->is_uniform) {
+        UniformScratch U{h->u_par.p, h->u_chi.p, h->u_lml.p, h->u_lamlog.p, (V + 31) / 32, h->nch_pad};
+        prm.stride = h->nch_pad;
+        const int ugrid = h->nch_pad / 128 + (h->nch_pad % 128 ? 1 : 0);
+        if (cx.replay) {
+            ReplaySource src{rp, C, V};
+            mh_uniform_kernel<ReplaySource><<<ugrid, 128, 0, h->stream>>>(h->dev, h->st, prm, src, U, h->x_d.p, h->x_t.p);
+        } else {
+            PhiloxSource src{h->seed, h->chain_offset};
+            mh_uniform_kernel<PhiloxSource><<<ugrid, 128, 0, h->stream>>>(h->dev, h->st, prm, src, U, h->x_d.p, h->x_t.p);
+        }
+    } else if (h->is_poly) {
         if (cx.replay) {
             ReplaySource src{rp, C, V};
             mh_poly_kernel<ReplaySource><<<h->poly_grid, 128, 0, h->stream>>>(h->dev, h->poly, h->st, prm, src, h->poly_arena.p, h->poly_warena.p, h->poly_mcap_p);

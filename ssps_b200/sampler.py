@@ -68,7 +68,7 @@ class Sampler:
     def __init__(self, device: int = -1, regression_deg: int = 1, large_indeg: float = 20.0,
                  lambda_max: float = 15.0, lambda_prop_std: float = 0.25, max_indegree: int = 0,
                  psrf_grid: int = 0, record_changepoints: bool = False, collect_khist: bool = False,
-                 verify: bool = False, min_burnin: float = 0.0, snapshot_slots: int = 0):
+                 verify: bool = False, min_burnin: float = 0.0, snapshot_slots: int = 0, proposal: str = "sparse"):
         self._L = _lib.load()
         cfg = Config()
         cfg.struct_size = C.sizeof(Config)
@@ -84,6 +84,9 @@ class Sampler:
         cfg.verify = int(verify)
         cfg.min_burnin = float(min_burnin)
         cfg.snapshot_slots = int(snapshot_slots)
+        if proposal not in ("sparse", "uniform"):
+            raise ValueError("proposal must be 'sparse' or 'uniform' (SSPS.jl:87-88)")
+        cfg.proposal = 1 if proposal == "uniform" else 0
         self._h = C.c_void_p()
         check(self._L.ssps_create(C.byref(cfg), C.byref(self._h)))
         self.cfg = cfg

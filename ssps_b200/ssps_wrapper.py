@@ -75,8 +75,15 @@ def perform_inference(timeseries_filename, ref_graph_filename, output_path, time
                       multithread, n_chains=1, seed=None, device=-1, posterior_json="", burnin=0.5, gpus=1,
                       no_chain_json=False):
     """perform_inference (SSPS.jl:135-233)."""
-    if proposal == "uniform" and not multithread:
-        raise SystemExit("--proposal uniform (deprecated in the reference, SSPS.jl:88) is not implemented")
+    if proposal not in ("sparse", "uniform"):
+        raise SystemExit("--proposal must be 'sparse' or 'uniform' (SSPS.jl:87-88)")
+    if multithread:
+        proposal = "sparse"             # "This flag overrides the --proposal argument, setting it to 'sparse'" (SSPS.jl:98)
+    if proposal == "uniform":
+        if regression_deg >= 2:
+            raise SystemExit("--proposal uniform (deprecated in the reference, SSPS.jl:88) is implemented for --regression-deg <= 1 only")
+        if gpus > 1:
+            raise SystemExit("--proposal uniform runs on one GPU (one thread per chain)")
     if regression_deg < 1:
         print("note: --regression-deg %d builds an EMPTY design in the reference (construct_B, dbn_distributions.jl:179-194): "
               "the likelihood is flat and only the edge prior acts.  Reproduced as is; every shipped config passes 1."
@@ -85,7 +92,7 @@ def perform_inference(timeseries_filename, ref_graph_filename, output_path, time
     print("Invoking SSPS on input files:\n\t%s\n\t%s" % (timeseries_filename, ref_graph_filename))
     t_start = time.time()
     kw = dict(regression_deg=regression_deg, large_indeg=large_indeg, lambda_max=lambda_max,
-              lambda_prop_std=lambda_prop_std, record_changepoints=not no_chain_json)
+              lambda_prop_std=lambda_prop_std, record_changepoints=not no_chain_json, proposal=proposal)
     if seed is None:
         seed = int(time.time_ns() & 0x7FFFFFFFFFFFFFFF)   # the reference never seeds its RNG either
     multi = gpus > 1

@@ -25,7 +25,7 @@ def test_header_symbols_are_exported_and_bound():
         assert hasattr(raw, n), "library does not export %s" % n
         assert n in _lib.SIGNATURES, "binding misses %s" % n
     assert set(_lib.SIGNATURES) == set(names)
-    assert L.ssps_abi_version() == 3
+    assert L.ssps_abi_version() == 4
     assert L.ssps_psrf_sums_len(10) == 3 * 100 + 30 + 2
 
 

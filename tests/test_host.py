@@ -74,8 +74,10 @@ def test_recover_state():
 
 def test_unsupported_modes_exit_loudly():
     from ssps_b200.ssps_wrapper import perform_inference
+    with pytest.raises(SystemExit):     # the deprecated uniform proposal exists for regression_deg <= 1 only
+        perform_inference("a", "b", "c", 1.0, 10, 1, 20.0, 15.0, 2, 0.25, "uniform", "", False)
     with pytest.raises(SystemExit):
-        perform_inference("a", "b", "c", 1.0, 10, 1, 20.0, 15.0, 1, 0.25, "uniform", "", False)
+        perform_inference("a", "b", "c", 1.0, 10, 1, 20.0, 15.0, 1, 0.25, "edge-reversal", "", False)
 
 
 def test_simulator_shapes_and_prior_edit_counts():
