@@ -24,6 +24,8 @@
  *        smart_proposal / smart_involution              SSPS/src/dbn_proposals.jl:60-130
  *        lambda_vec_proposal                            SSPS/src/dbn_proposals.jl:244-248
  *        Gen.mh acceptance (Gen 0.4.5, not in tree)     call sites state_updates.jl:44-47
+ *        config.proposal = 1: uniform_update_loop       SSPS/src/state_updates.jl:98-112
+ *        unpaired_edges / uniform_proposal / _involution SSPS/src/dbn_proposals.jl:142-230
  *   ssps_export_draws
  *        the stream of Gen.normal / rand() / categorical / uniform_discrete draws of the sweep
  *        (Gen 0.4.5 samplers; call sites SSPS/src/dbn_proposals.jl:67-77,246)
@@ -34,6 +36,11 @@
  *        update_results_storediff                       SSPS/src/state_updates.jl:161-227
  *   ssps_psrf / ssps_psrf_sums / ssps_psrf_finish
  *        evaluate_convergence / compute_psrf_neff       scripts/postprocess_samples.jl:99-180
+ *   ssps_convergence
+ *        correlation_sum / compute_psrf_neff (N_eff)    scripts/postprocess_samples.jl:58-138
+ *        evaluate_convergence / evaluate_summary        scripts/postprocess_samples.jl:155-191
+ *   ssps_comm_* / ssps_run_multi / ssps_*_global
+ *        pooling of per-chain JSON files                scripts/postprocess_samples.jl:242-259
  *
  * Conventions: all indices 0-based (the 1-based <-> 0-based shift lives in the language shim);
  * matrices column-major; the caller owns every buffer passed in or out (inputs are copied to the
@@ -284,6 +291,9 @@ int  ssps_measure_gather_peak(ssps_handle* h, int64_t table_bytes, double* l1_gb
  * shapes (cudaMalloc of the 100 MB-class buffers costs 2..100 ms).  This returns the cached blocks of `device` to the
  * driver; live handles are not affected.  No counterpart in the reference (Julia's GC owns its memory). */
 int  ssps_release_cached_memory(int32_t device);
+/* Debug builds only (-DSSPS_BOUNDS: index checks on every scratch / Stage / slot accessor of the kernels): number of failed
+ * checks since the library was loaded, on the current device; -1 = the library was built without the checks. */
+int64_t ssps_bounds_failures(void);
 
 #ifdef __cplusplus
 }

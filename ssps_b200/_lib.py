@@ -92,6 +92,7 @@ SIGNATURES = {
     "ssps_measure_fp64_peak": (C.c_int, [_hp, _dp]),
     "ssps_measure_gather_peak": (C.c_int, [_hp, C.c_int64, _dp, _dp, _dp]),
     "ssps_release_cached_memory": (C.c_int, [C.c_int32]),
+    "ssps_bounds_failures": (C.c_int64, []),
 }
 
 _lib = None

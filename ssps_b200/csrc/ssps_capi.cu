@@ -994,7 +994,8 @@ int run_launch(ssps_handle* h, RunCtx& cx) {
     if (h->snap_grid > 0) rec = std::min(rec, h->snap_grid - h->samples_recorded % h->snap_grid);
     // no measured task costs yet: a short calibration launch, so that the scheduler can split the heavy vertices for the rest
     // of the batch (the first 100-sweep launch of a fresh handle ran 25 % longer than the later ones)
-    if (!h->have_cost && !cx.replay && rec > 24 && !h->is_uniform && !h->is_poly) rec = 8;
+    static const int calib = getenv("SSPS_CALIB_SWEEPS") ? atoi(getenv("SSPS_CALIB_SWEEPS")) : 8;      // experiments: 0 = no calibration launch
+    if (!h->have_cost && !cx.replay && rec > 24 && !h->is_uniform && !h->is_poly && calib > 0) rec = calib;
     const int n_local = (int)(rec * thinning);
     MhParams prm{};
     prm.sweep0 = h->sweeps_done; prm.n_local = n_local; prm.thinning = thinning;
@@ -1557,6 +1558,16 @@ int ssps_get_vertex_cost(ssps_handle* h, int64_t* cycles, int32_t* mean_indeg_x1
         }
     }
     return SSPS_OK;
+}
+
+int64_t ssps_bounds_failures(void) {
+#ifdef SSPS_BOUNDS
+    unsigned long long v = 0;
+    if (cudaMemcpyFromSymbol(&v, g_ssps_bounds_fail, sizeof v) != cudaSuccess) { cudaGetLastError(); return -2; }
+    return (int64_t)v;
+#else
+    return -1;
+#endif
 }
 
 int ssps_release_cached_memory(int32_t device) {

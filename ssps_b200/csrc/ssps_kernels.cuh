@@ -82,15 +82,25 @@ __device__ __forceinline__ double u53_to_unit(uint32_t hi, uint32_t lo) {
 // interleaved across threads so that a warp touching the same logical index is conflict-free /
 // coalesced.  Two homes: shared memory (|S'| <= SSPS_KS) and a global arena (larger sets).
 // ------------------------------------------------------------------------------------------------
+// -DSSPS_BOUNDS: index checks on the scratch / Stage / slot accessors, counted in a device symbol (ssps_bounds_failures).
+// compute-sanitizer is closed on the build pool; this is the memcheck stand-in that the GPU test suite is run under
+// (tools/bounds_run.sh, profiles/r2_bounds_check.txt).
+#ifdef SSPS_BOUNDS
+__device__ unsigned long long g_ssps_bounds_fail = 0ull;
+#define SSPS_CHK(cond) do { if (!(cond)) atomicAdd(&g_ssps_bounds_fail, 1ull); } while (0)
+#else
+#define SSPS_CHK(cond) do { } while (0)
+#endif
+
 struct Scratch {
     double* d;        // &arena[tid], logical index e lives at d[e * stride]
     uint16_t* t;      // &tarena[tid]
     int stride;
     int kcap;         // capacity in rows
-    __device__ __forceinline__ double& L(int e) const { return d[(size_t)e * stride]; }
-    __device__ __forceinline__ double& w(int a) const { return d[(size_t)(SSPS_TRI(kcap) + a) * stride]; }
-    __device__ __forceinline__ uint16_t& T(int a) const { return t[(size_t)a * stride]; }
-    __device__ __forceinline__ uint16_t& S(int a) const { return t[(size_t)(kcap + a) * stride]; }   // second id list (K3 only)
+    __device__ __forceinline__ double& L(int e) const { SSPS_CHK(e >= 0 && e < SSPS_TRI(kcap)); return d[(size_t)e * stride]; }
+    __device__ __forceinline__ double& w(int a) const { SSPS_CHK(a >= 0 && a < kcap); return d[(size_t)(SSPS_TRI(kcap) + a) * stride]; }
+    __device__ __forceinline__ uint16_t& T(int a) const { SSPS_CHK(a >= 0 && a < kcap); return t[(size_t)a * stride]; }
+    __device__ __forceinline__ uint16_t& S(int a) const { SSPS_CHK(a >= 0 && a < kcap); return t[(size_t)(kcap + a) * stride]; }   // second id list (K3 only)
 };
 
 // lml(child, S') for the sorted set held in sc.T(0..kn-1).  Mirrors orc_lml_chol operation for
@@ -298,6 +308,7 @@ struct ChainState {
 };
 
 __device__ __forceinline__ uint32_t& slot_ref(const ChainState& st, int V, int vertex, int a, int chain) {
+    SSPS_CHK(vertex >= 0 && vertex < V && a >= 0 && a < V && chain >= 0 && chain < st.nch_pad);
     return st.slots[((size_t)vertex * V + a) * st.nch_pad + chain];
 }
 

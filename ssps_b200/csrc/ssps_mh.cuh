@@ -172,7 +172,7 @@ struct SmallAcc {   // shared memory, element-major: [e][thread]
 struct BigRef {
     double* f; uint32_t* w; uint16_t* r; int kcap;
     __device__ __forceinline__ double* fw() const { return f + SSPS_TRI(kcap); }
-    __device__ __forceinline__ int id(int a) const { return (int)(w[a] & 0xffffu); }
+    __device__ __forceinline__ int id(int a) const { SSPS_CHK(a >= 0 && a < kcap); return (int)(w[a] & 0xffffu); }
 };
 
 // The warp's working copy of ONE lane's BIG-tier state while the warp works on it: shared memory when
@@ -186,7 +186,7 @@ struct Stage {
     double* tw;         // w
     uint32_t* id;       // id | rel << 16, arrival order
     uint16_t* rk;       // sorted rank
-    __device__ __forceinline__ int idof(int a) const { return (int)(id[a] & 0xffffu); }
+    __device__ __forceinline__ int idof(int a) const { SSPS_CHK(a >= 0 && a < 32 * SSPS_KU); return (int)(id[a] & 0xffffu); }
 };
 
 // Entry e of a Stage's factor rows / w vector.  SH = the Stage is the warp's shared-memory one: the accesses index the
@@ -196,8 +196,8 @@ template <bool SH>
 struct StageAcc {
     double* tp; double* wp; unsigned toff, woff;
     __device__ __forceinline__ explicit StageAcc(const Stage& T) : tp(T.t), wp(T.tw), toff(SH ? (unsigned)(T.t - ssps_smem) : 0u), woff(SH ? (unsigned)(T.tw - ssps_smem) : 0u) {}
-    __device__ __forceinline__ double& t(int e) const { if (SH) return ssps_smem[toff + e]; return tp[e]; }
-    __device__ __forceinline__ double& w(int e) const { if (SH) return ssps_smem[woff + e]; return wp[e]; }
+    __device__ __forceinline__ double& t(int e) const { SSPS_CHK(e >= 0 && (!SH || e < SSPS_TRI(SSPS_KST))); if (SH) return ssps_smem[toff + e]; return tp[e]; }
+    __device__ __forceinline__ double& w(int e) const { SSPS_CHK(e >= 0 && (!SH || e < SSPS_KST)); if (SH) return ssps_smem[woff + e]; return wp[e]; }
 };
 
 // dynamic shared memory of one CTA: SMALL-tier slots of every thread + one Stage per warp
@@ -736,7 +736,11 @@ __device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const S
     const bool on = src >= 0;
     const int srcl = on ? src : s0;
     const unsigned foff = (unsigned)(C.st_smem.t - ssps_smem) + (unsigned)half * SSPS_MID_SLOT;
+#ifdef SSPS_BOUNDS
+#define FS(e) (*[&](int e_) -> double* { SSPS_CHK(e_ >= 0 && e_ < SSPS_ROWLEN(SSPS_KM)); return &ssps_smem[foff + e_]; }(e))
+#else
 #define FS(e) ssps_smem[foff + (e)]
+#endif
 #define FW(e) FS(SSPS_TRI(SSPS_KM) + (e))
     uint32_t* const Fid = (uint32_t*)(ssps_smem + foff + SSPS_ROWLEN(SSPS_KM));      // id | rel << 16, arrival order (the CURRENT set until the commit)
     uint16_t* const Frk = (uint16_t*)(Fid + SSPS_KM);                                 // sorted ranks

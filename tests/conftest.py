@@ -44,3 +44,18 @@ def make_synth(V, T=8, M=4, seed=20200701):
 def synth_v1000():
     """V = 1000, T = 100, M = 4 (n = 396): the shape of BASELINE.json's config C5 (and of the V = 1000 replay test)."""
     return make_synth(1000, T=100, M=4)
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """A library built with -DSSPS_BOUNDS (tools/bounds_run.sh) counts failed index checks on the device: report them."""
+    try:
+        from ssps_b200 import _lib
+        if _lib._lib is None:
+            return
+        n = _lib._lib.ssps_bounds_failures()
+    except Exception:
+        return
+    if n >= 0:
+        print("\n[ssps bounds check] failed index checks on the device: %d" % n)
+        if n > 0:
+            session.exitstatus = 1
