@@ -430,7 +430,36 @@ __device__ __forceinline__ bool mh_accept(const SspsDev& P, const int action, co
     return accept;
 }
 
-// out-of-line copy for the rare tiers (mid_move, big_phase): 320 instructions per inlined instance
+// the rare tiers (mid_pair, big_phase): the screening inline (60 instructions), the reference-order test out of line.
+// (A fully out-of-line copy of mh_accept cost 2 300 cycles per MID pass: 320 cold instructions for a test that the
+// screening decides 99.9995 % of the time.)
+template <bool VERIFY>
+__device__ __forceinline__ bool mh_accept_rare(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
+                                               const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
+                                               const double ip_new, const float lg_new, const double u_acc, unsigned long long* stats) {
+    const float lgu = fast_lg2((float)u_acc);
+    const double hn = 0.5 * P.dn;
+    const double base = ((dprior - fwd) + bwd) - 0.5 * (double)(kn - k) * P.log1pn;
+    const double diff = SSPS_LN2 * ((double)lgu + hn * ((double)lg_new - (double)lg_ip_cur)) - base;
+    const double marg = 1.2e-6 * ((double)fabsf(lgu) + 1.0 + hn * ((double)(fabsf(lg_new) + fabsf(lg_ip_cur)) + 2.0)) + 1e-9 * fabs(base) + 1e-6;
+    bool accept = diff < 0.0;
+    const bool close = !(u_acc > 1e-30 && fabs(diff) > marg);
+    if (close || VERIFY) {
+        const bool ex = mh_accept_exact(P.log1pn, P.dn, action, k, kn, dprior, fwd, bwd, ip_cur, ip_new, u_acc) != 0;
+        if (close) { atomicAdd(stats + ST_TIER1, 1ull); accept = ex; }
+        else {
+            if (ex != accept) atomicAdd(stats + ST_DEC_MISMATCH, 1ull);
+            // how much of its margin the screening used (a flip needs a ratio above 1); the exact difference is re-formed here
+            const double lml_cur = -0.5 * (double)k * P.log1pn - 0.5 * P.dn * log(ip_cur);
+            const double lml_new = -0.5 * (double)kn * P.log1pn - 0.5 * P.dn * log(ip_new);
+            const double w = dprior + (lml_new - lml_cur);
+            const double alpha = (action == ACT_SWAP) ? w : ((w - fwd) + bwd);
+            atomicMax((unsigned*)(stats + ST_MARGIN_USE), __float_as_uint((float)(fabs(diff - (log(u_acc) - alpha)) / marg)));
+        }
+    }
+    return accept;
+}
+
 template <bool VERIFY>
 __device__ __noinline__ bool mh_accept_ool(const SspsDev& P, const int action, const int k, const int kn, const double dprior,
                                            const double fwd, const double bwd, const double ip_cur, const float lg_ip_cur,
@@ -750,10 +779,16 @@ __device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const S
     const int a_ord = __shfl_sync(SSPS_FULL, mv.a_ord, srcl);
     const int r_ord = __shfl_sync(SSPS_FULL, mv.r_ord, srcl);
     const BigRef B = C.big(srcl);
+#ifdef SSPS_PROFILE_BIG
+    long long tp_ = clock64();
+#endif
     if (on) {       // the subject's factor, ids and ranks into the slot
         for (int e = hl; e < SSPS_TRI(k); e += 16) FS(e) = B.f[e];
         if (hl < k) { FW(hl) = B.fw()[hl]; Fid[hl] = B.w[hl]; Frk[hl] = B.r[hl]; }
     }
+#ifdef SSPS_PROFILE_BIG
+    { const long long tn_ = clock64(); if (lane == 0) atomicAdd(C.stats + ST_MID_PROF + 0, (unsigned long long)(tn_ - tp_)); tp_ = tn_; }
+#endif
     __syncwarp();
     const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
     const unsigned hshift = 16u * (unsigned)half;
@@ -777,7 +812,37 @@ __device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const S
 #pragma unroll 1
         for (int m = 0; m < p && m < kr; ++m) { const double wm = FW(m); q_new = fma(wm, wm, q_new); }
     }
+#ifdef SSPS_PROFILE_BIG
+    { const long long tn_ = clock64(); if (lane == 0) atomicAdd(C.stats + ST_MID_PROF + 1, (unsigned long long)(tn_ - tp_)); tp_ = tn_; }
+#endif
+    // All gathers of the pass first, back to back (an L2 round trip each when they miss: one latency instead of one per row):
+    // lane r of the half fetches G_jj and r_j of row p + r into registers; lane c fetches the seeds G(j_a, id_c) of its column
+    // for every row below it -- into the row's own slot entries (dead: they are about to be recomputed), the arriving row's
+    // into the spare third slot of the Stage (its slot still holds cached entries the row above it reads).
+#define SCR(e) ssps_smem[(unsigned)(C.st_smem.t - ssps_smem) + 2u * SSPS_MID_SLOT + 16u * (unsigned)half + (e)]
+    double ga_own = 1.0, t_own = 0.0;
+    if (work) {
+        const int a_own = p + hl;
+        if (a_own < kn) {
+            const int ja = (a_own == kr) ? j_add : (int)(Fid[a_own + 1] & 0xffffu);
+            ga_own = __ldg(P.G + (size_t)ja * V + ja); t_own = __ldg(Ri + ja);
+        }
+        if (hl < kr) {
+            const int idc = (int)(Fid[hl + (hl >= p ? 1 : 0)] & 0xffffu);
+#pragma unroll 1
+            for (int a = max(p, hl + 1); a < kn; ++a) {
+                const bool arr = a == kr;
+                if (!arr && hl < p) continue;                   // left of the removed column: the cached entry
+                const int ja = arr ? j_add : (int)(Fid[a + 1] & 0xffffu);
+                const double g = __ldg(P.G + (size_t)ja * V + idc);
+                if (arr) SCR(hl) = g; else FS(SSPS_TRI(a) + hl) = g;
+            }
+        }
+    }
+    __syncwarp();
     // rows [p, kn) of the proposed set; the row loop is warp-uniform (shuffles inside), a half works on the rows of its own range
+    const unsigned myrow = foff + (unsigned)SSPS_TRI(hl);           // lane c = hl owns column c: l_cb is entry b of (new) row c
+    double inv_own = (work && hl < p) ? ssps_smem[myrow + hl] : 0.0;        // 1/d of row hl; rows >= p get theirs as they are recomputed
     const int a_lo = work ? p : (1 << 20), a_hi = work ? kn : 0;
     const int a_min = min(a_lo, __shfl_xor_sync(SSPS_FULL, a_lo, 16)), a_max = max(a_hi, __shfl_xor_sync(SSPS_FULL, a_hi, 16));
 #pragma unroll 1
@@ -786,23 +851,20 @@ __device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const S
         const bool arr = a == kr;                               // the arriving parent's row (nothing cached)
         const int c0 = arr ? 0 : p;
         const int xa = SSPS_TRI(a), olda = SSPS_TRI(a + 1);
-        int ja = 0;
-        double sc = 0.0, gaa = 1.0, t = 0.0;
-        if (act) {
-            ja = arr ? j_add : (int)(Fid[a + 1] & 0xffffu);
-            const double* __restrict__ Ga = P.G + (size_t)ja * V;
-            if (hl >= c0 && hl < a) sc = __ldg(Ga + (int)(Fid[hl + (hl >= p ? 1 : 0)] & 0xffffu));
-            gaa = __ldg(Ga + ja); t = __ldg(Ri + ja);
-        }
+        const double gaa = __shfl_sync(SSPS_FULL, ga_own, (a - p) & 15, 16);
+        double t = __shfl_sync(SSPS_FULL, t_own, (a - p) & 15, 16);
+        double sc = 0.0;
+        if (act && hl >= c0 && hl < a) sc = arr ? SCR(hl) : FS(xa + hl);
         double d2 = gaa;
+        // Step b: lane b scales its own s_b by ITS row's 1/d (held in a register: no load on the chain) and hands it round;
+        // the dependent chain per step is  multiply -> shuffle -> fma.
 #pragma unroll 1
         for (int b = 0; b < a; ++b) {
-            const double invb = FS(SSPS_TRI(b) + b), wb = FW(b);
-            const double lsh = __shfl_sync(SSPS_FULL, sc * invb, b, 16);
+            const double lsh = __shfl_sync(SSPS_FULL, sc * inv_own, b, 16);
             if (act) {
                 const double l = (b < c0) ? FS(olda + b) : lsh;
-                d2 = fma(-l, l, d2); t = fma(-l, wb, t);
-                if (hl > b && hl >= c0 && hl < a) sc = fma(-l, FS(SSPS_TRI(hl) + b), sc);
+                d2 = fma(-l, l, d2); t = fma(-l, FW(b), t);
+                if (hl > b && hl >= c0 && hl < a) sc = fma(-l, ssps_smem[myrow + b], sc);
                 if (hl == b) FS(xa + b) = l;
             }
         }
@@ -812,9 +874,13 @@ __device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const S
             else if (d2 != d2 || gaa != gaa) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; }
             q_new = fma(w, w, q_new);
             if (hl == 0) { FS(xa + a) = inv; FW(a) = w; }
+            if (hl == a) inv_own = inv;
         }
         __syncwarp();
     }
+#ifdef SSPS_PROFILE_BIG
+    { const long long tn_ = clock64(); if (lane == 0) atomicAdd(C.stats + ST_MID_PROF + 3, (unsigned long long)(tn_ - tp_)); tp_ = tn_; }
+#endif
     // ---- the subject lanes: acceptance (they may sit in either half: the move's numbers come from lane 0 of the half that did the work) ----
     const int wh = (lane == s1) ? 16 : 0;
     const double q_s = __shfl_sync(SSPS_FULL, q_new, wh);
@@ -834,7 +900,7 @@ __device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const S
             if (rem_s) { omc_rem = __ldg(omc_i + jrem_s); dprior = dprior + L.lam * omc_rem; }
             const double ip_new = C.yty - P.shrink * q_s;
             const float lg_new = fast_lg2((float)ip_new);
-            acc = mh_accept_ool<VERIFY>(P, act_s, ks, kn_s, dprior, mv.fwd, mv.bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats) ? 1 : 0;
+            acc = mh_accept_rare<VERIFY>(P, act_s, ks, kn_s, dprior, mv.fwd, mv.bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats) ? 1 : 0;
             if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
                 const uint32_t* ids_s = (const uint32_t*)(ssps_smem + (unsigned)(C.st_smem.t - ssps_smem) + (unsigned)(wh >> 4) * SSPS_MID_SLOT + SSPS_ROWLEN(SSPS_KM));
                 int tt = 0;
@@ -862,6 +928,9 @@ __device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const S
             *acc_kn = acc | (kn_s << 1);
         }
     }
+#ifdef SSPS_PROFILE_BIG
+    { const long long tn_ = clock64(); if (lane == 0) atomicAdd(C.stats + ST_MID_PROF + 4, (unsigned long long)(tn_ - tp_)); tp_ = tn_; }
+#endif
     // ---- commit (the half that did the work): ids with the gap at p closed and the sorted ranks shifted, rows [p, kn) ----
     const int acc_h = __shfl_sync(SSPS_FULL, acc, srcl);
     if (on && acc_h) {
@@ -885,11 +954,18 @@ __device__ __noinline__ Lane mid_pair(const SspsDev& P, const int child, const S
             if (hl >= p && hl < kn) fw[hl] = FW(hl);
         }
     }
+#ifdef SSPS_PROFILE_BIG
+    { const long long tn_ = clock64(); if (lane == 0) atomicAdd(C.stats + ST_MID_PROF + 5, (unsigned long long)(tn_ - tp_)); tp_ = tn_; }
+#endif
     __syncwarp();
+#ifdef SSPS_PROFILE_BIG
+    if (lane == 0) { atomicAdd(C.stats + ST_MID_PROF + 6, (unsigned long long)max(a_max - a_min, 0)); atomicAdd(C.stats + ST_MID_PROF + 7, 1ull); }
+#endif
     if (lane == 0) atomicAdd(C.stats + ST_MID_STEPS, (unsigned long long)(1 + (s1 >= 0 ? 1 : 0)));
     return L;
 #undef FS
 #undef FW
+#undef SCR
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1300,7 +1376,7 @@ __device__ __noinline__ Lane big_phase(const SspsDev& P, const int child, const 
             if (has_rem) { omc_rem = __ldg(omc_i + j_rem); dprior = dprior + L.lam * omc_rem; }
             const double ip_new = C.yty - P.shrink * q_new;
             const float lg_new = fast_lg2((float)ip_new);
-            acc = mh_accept_ool<VERIFY>(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats) ? 1 : 0;
+            acc = mh_accept_rare<VERIFY>(P, action, k, kn, dprior, fwd, bwd, L.ip, L.lg_ip, ip_new, lg_new, d.u_acc, C.stats) ? 1 : 0;
             if (VERIFY) {       // the proposed set's q from scratch, in its arrival order: must be the same bits
                 const Scratch xs = C.xs_of(lane);
                 for (int b = 0; b < kn; ++b) xs.T(b) = (uint16_t)T.idof(b);

@@ -42,8 +42,9 @@ with Sampler(large_indeg=15.0, lambda_prop_std=3.0, psrf_grid=max(S // 4, 1), ve
         print("khist:", s.khist(40).tolist())
     if os.environ.get('DIAG_PROF'):
         r = s.raw_stats(48)
-        if r[34]:
-            print("MID: %d passes (two lanes each at most), %.0f cycles per pass, %.0f per lane-step" % (r[34], r[15] / r[34], r[15] / max(r[14], 1)))
+        if r[39]:
+            print("MID: %d passes (two lanes each at most), %.0f cycles per pass, %.0f per lane-step | per pass: copy-in %.0f, scans+prefix %.0f, rows %.0f (%.1f rows), accept %.0f, commit %.0f"
+                  % (r[39], r[15] / r[39], r[15] / max(r[14], 1), r[32] / r[39], r[33] / r[39], r[35] / r[39], r[38] / r[39], r[36] / r[39], r[37] / r[39]))
         names = ["select+bcast", "stage_load", "scans", "remove (+q prefix)", "append", "accept (src lane)", "commit", "promote+tail"]
         tot = float(r[16:24].sum()) or 1.0
         print("BIG phase cycles by section (profiling build): " + ", ".join("%s %.1f%%" % (n, 100 * r[16 + e] / tot) for e, n in enumerate(names)),
