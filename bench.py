@@ -375,7 +375,8 @@ def run_ours(args, rank, world, local_rank):
             "hbm": hbm_view(traffic, k_ms / max(launches, 1)),
             "ncu": None if ncu is None else {k: ncu[k] for k in ("source", "launch", "issue_slot_utilisation_pct", "fp64_pipe_active_pct",
                                                                 "warp_instructions_per_launch", "stall_cycles_per_issue",
-                                                                "l1_hit_pct", "l2_hit_pct", "registers_per_thread")}})
+                                                                "l1_hit_pct", "l2_hit_pct", "registers_per_thread",
+                                                                "active_lanes_per_instruction", "eligible_warps_per_cycle") if k in ncu}})
 
     # ---- e2e: host buffers in, posterior out, every step ----
     e2e = None

@@ -26,6 +26,8 @@ d = {
     "stall_cycles_per_issue": {k: get("smsp__average_warps_issue_stalled_%s_per_issue_active.ratio" % k)
                                for k in ("no_instruction", "long_scoreboard", "wait", "barrier", "branch_resolving", "short_scoreboard", "selected")},
     "registers_per_thread": get("launch__registers_per_thread"),
+    "active_lanes_per_instruction": get("smsp__thread_inst_executed_per_inst_executed.ratio"),
+    "eligible_warps_per_cycle": get("smsp__warps_eligible.avg.per_cycle_active"),
 }
 json.dump(d, open(out_path, "w"), indent=1)
 print(json.dumps(d, indent=1))
