@@ -89,6 +89,11 @@ def run_reference(args, rank, world):
     host core.  The Julia reference itself cannot run here (no julia binary)."""
     if rank != 0:
         return
+    if args.workload == "c5":
+        # construct_B of a model-drawn start is 396 x 2^k for k up to ~20: neither Julia nor its restatement can build it
+        emit_line(json.dumps({"impl": "reference", "unavailable": "config C5 (V=1000, regression_deg full): the reference's algorithm builds the design "
+                              "explicitly and cannot score the model-drawn initial sets (2^k - 1 columns, k up to ~20); no CPU figure exists"}))
+        return
     from oracle import oracle as orc
     ds, xm, xp = make_workload(args.V, args.T, args.M)
     P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, regression_deg=args.deg)
