@@ -399,6 +399,7 @@ int finish_data(ssps_handle* h, const double* prior_host) {
         d.log1pn = 0.0;
     }
     h->poly.Xminus = h->Xminus.p; h->poly.Y = h->Y.p; h->poly.deg = h->cfg.regression_deg;
+    h->poly.force_warp = getenv("SSPS_POLY_FORCE_WARP") != nullptr;
     h->has_data = true;
     // any chains belong to the previous data set
     h->n_chains = 0;
@@ -581,7 +582,7 @@ int ssps_score(ssps_handle* h, int32_t n_sets, const int32_t* child, const int32
         for (int s = 0; s < n_sets; ++s) {
             const int k = set_offsets[s + 1] - set_offsets[s];
             int m = 0;
-            const int cls = poly_class(k, h->cfg.regression_deg, h->n, m);
+            const int cls = poly_class(k, h->poly, h->n, m);
             if (cls == PC_REFUSE || (cls != PC_SAT && cls != PC_EMPTY && k > SSPS_POLY_KLIST))
                 return fail(SSPS_ERR_UNSUPPORTED, "regression_deg=%d: set %d has %d parents and a design of fewer than n - 1 = %d columns; "
                             "the interaction-column scorer handles at most %d parents for such sets", h->cfg.regression_deg, s, k, h->n - 1, SSPS_POLY_KW);
@@ -752,7 +753,7 @@ int alloc_chains(ssps_handle* h, int n_chains) {
         // WARP tier: scratch for the widest design a set within max_indegree can have below saturation (csrc/ssps_poly.cuh);
         // the grid shrinks if that scratch would take more than a quarter of the free memory
         const int m_scored = poly_max_scored_width(std::min(h->kcap, SSPS_POLY_KLIST), h->cfg.regression_deg, h->n);
-        h->poly_mcap_p = m_scored > SSPS_POLY_MMAX ? ((m_scored + 31) & ~31) : 0;
+        h->poly_mcap_p = (m_scored > SSPS_POLY_MMAX || (h->poly.force_warp && m_scored > 0)) ? ((m_scored + 31) & ~31) : 0;
         const size_t wdoubles = poly_warp_scratch_doubles(h->n, h->poly_mcap_p);
         if (h->poly_mcap_p) {
             size_t free_b = 0, total_b = 0;

@@ -46,6 +46,7 @@ struct PolyDev {
     const double* Xminus;          // n x V column-major, RAW
     const double* Y;               // n x V column-major, standardised
     int deg;                       // regression_deg (>= 2 on this path)
+    int force_warp;                // test hook (SSPS_POLY_FORCE_WARP): sets of the THREAD class go through the WARP tier -- same bits
 };
 
 // design width sum_{d = 1..min(deg, k)} C(k, d), exact while <= limit; limit + 1 as soon as it exceeds the limit
@@ -77,6 +78,10 @@ __host__ __device__ inline int poly_class(int k, int deg, int n, int& m_out) {
     m_out = (int)m;
     if (m <= SSPS_POLY_MMAX && k <= SSPS_POLY_KMAX) return PC_THREAD;
     return k <= SSPS_POLY_KW ? PC_WARP : PC_REFUSE;
+}
+__host__ __device__ inline int poly_class(int k, const PolyDev& Q, int n, int& m_out) {
+    const int c = poly_class(k, Q.deg, n, m_out);
+    return (c == PC_THREAD && Q.force_warp) ? PC_WARP : c;
 }
 // widest numerically scored design any set of at most kcap parents can have (sizes the WARP tier's scratch)
 inline int poly_max_scored_width(int kcap, int deg, int n) {
@@ -281,34 +286,51 @@ __device__ __noinline__ double poly_score_warp(const SspsDev& P, const PolyDev& 
         rhs[c] = r;
     }
     __syncwarp();
-    // Gram matrix of the centred columns: tiles of 4 rows x (4 x 32) columns, every entry one lane's ascending-t fma chain
-    for (int c0 = 0; c0 < m; c0 += 4) {
-        const int jend = (min(c0 + 3, m - 1) >> 5) + 1;             // column chunks that hold some b <= c
-        for (int jb = 0; jb < jend; jb += 4) {
-            double acc[4][4];
+    // Gram matrix of the centred columns.  Tiles of 16 rows x 32 columns: every entry is one lane's ascending-t fma chain
+    // (the THREAD tier's bits); per t a lane loads ONE value of its own column and the tile's 16 row values come as eight
+    // warp-uniform 16-byte loads, so the centred columns are streamed from L2 once per 16 rows of the matrix (the first
+    // version, 4 x 128 tiles, read them once per 4 rows: 33 MB per 255-column set, the bound of the whole scorer).
+    for (int c0 = 0; c0 < m; c0 += 16) {
+        const int jend = (min(c0 + 15, m - 1) >> 5) + 1;            // column chunks that hold some b <= c
+        for (int jb = 0; jb < jend; ++jb) {
+            double acc[16];
 #pragma unroll
-            for (int r = 0; r < 4; ++r)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) acc[r][j] = 0.0;
+            for (int r = 0; r < 16; ++r) acc[r] = 0.0;
             const double* row = cv;
-            for (int t = 0; t < n; ++t, row += mp) {
-                double bc[4], col[4];
+            const int b = lane + 32 * jb;
+            // eight rows of t in flight: the scratch of ~1 000 resident warps (1.3 MB each at C5) lives in HBM, and two rows
+            // in flight per warp left the loop waiting on DRAM latency (measured: 40e6 cycles per 255-column set)
+            int t = 0;
+            for (; t + 8 <= n; t += 8, row += 8 * (size_t)mp) {
+                double col[8];
 #pragma unroll
-                for (int r = 0; r < 4; ++r) bc[r] = row[c0 + r];         // c0 + 3 < mp: padding columns are zero
+                for (int u = 0; u < 8; ++u) col[u] = row[(size_t)u * mp + b];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) col[j] = (jb + j < nj) ? row[lane + 32 * (jb + j)] : 0.0;
+                for (int u = 0; u < 8; ++u) {
+                    const double2* bc = reinterpret_cast<const double2*>(row + (size_t)u * mp + c0);     // c0 + 15 < mp: padding columns are zero
 #pragma unroll
-                for (int r = 0; r < 4; ++r)
+                    for (int r = 0; r < 8; ++r) {
+                        const double2 v = bc[r];
+                        acc[2 * r] = fma(v.x, col[u], acc[2 * r]);
+                        acc[2 * r + 1] = fma(v.y, col[u], acc[2 * r + 1]);
+                    }
+                }
+            }
+            for (; t < n; ++t, row += mp) {
+                const double col = row[b];
+                const double2* bc = reinterpret_cast<const double2*>(row + c0);
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) acc[r][j] = fma(bc[r], col[j], acc[r][j]);
+                for (int r = 0; r < 8; ++r) {
+                    const double2 v = bc[r];
+                    acc[2 * r] = fma(v.x, col, acc[2 * r]);
+                    acc[2 * r + 1] = fma(v.y, col, acc[2 * r + 1]);
+                }
             }
 #pragma unroll
-            for (int r = 0; r < 4; ++r)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int c = c0 + r, b = lane + 32 * (jb + j);
-                    if (c < m && b <= c) g[(size_t)c * mp + b] = acc[r][j];
-                }
+            for (int r = 0; r < 16; ++r) {
+                const int c = c0 + r;
+                if (c < m && b <= c) g[(size_t)c * mp + b] = acc[r];
+            }
         }
     }
     __syncwarp();
@@ -323,37 +345,72 @@ __device__ __noinline__ double poly_score_warp(const SspsDev& P, const PolyDev& 
     __syncwarp();
     for (int c = lane; c < m; c += 32) gd[c] = g[(size_t)c * mp + c];
     __syncwarp();
-    // pivot-skipping Cholesky, right-looking: entry (a, b) receives  - l_ap l_bp  for p = 0, 1, .. in ascending order through fma
-    // (the diagonal and the rhs entry of row a are entries of that row: d2_a -= l_ap^2, t_a -= l_ap w_p)
+    // Pivot-skipping Cholesky in block columns of 32.  Entry (a, b), b <= a, receives  - l_ap l_bp  for p = 0, 1, .. b - 1 in
+    // ascending order through fma (the diagonal and the rhs entry of a row are entries of that row: d2_a -= l_ap^2,
+    // t_a -= l_ap w_p) -- the THREAD tier's order.  For the block column [b0, b0 + 32):
+    //   (1) the pivots p < b0, LEFT-looking: a lane owns column b0 + lane, sixteen rows per pass in registers, the scaled
+    //       columns l_.p read from the transposed copy kept in the otherwise unused upper triangle of g (row p: contiguous);
+    //   (2) the block's own 32 pivots, right-looking inside the block column ((m - b0) x 32 entries: L1-resident).
+    // The first version was right-looking over the whole trailing matrix: m^3/3 read-modify-writes through L2 (44 MB for a
+    // 255-column set); this one reads the finished columns once per 16 rows (3 MB).
     double q = 0.0;
-    for (int p = 0; p < m; ++p) {
-        const double d2 = g[(size_t)p * mp + p], tt = rhs[p], gaa = gd[p];
-        double inv, w;
-        if (d2 > SSPS_PIVOT_TOL * gaa) { inv = poly_inv_sqrt(d2); w = tt * inv; q = fma(w, w, q); }
-        else if (d2 != d2 || gaa != gaa) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; q = inv; }
-        else continue;                                  // numerically dependent column: l_ap = 0 for every a, nothing to subtract
-        for (int a = p + 1 + lane; a < m; a += 32) colp[a] = g[(size_t)a * mp + p] * inv;
-        __syncwarp();
-        for (int a = p + 1 + lane; a < m; a += 32) rhs[a] = fma(-colp[a], w, rhs[a]);
-        // trailing rows: lanes over b within a row, four rows in flight
-        for (int bb = p + 1; bb < m; bb += 32) {
-            const int b = bb + lane;
-            const double lb = b < m ? colp[b] : 0.0;
-            int a = bb;
-            for (; a + 3 < m; a += 4) {
-                const double l0 = colp[a], l1 = colp[a + 1], l2 = colp[a + 2], l3 = colp[a + 3];
-                double* r0 = g + (size_t)a * mp;
-                if (b <= a) r0[b] = fma(-l0, lb, r0[b]);
-                if (b <= a + 1) r0[mp + b] = fma(-l1, lb, r0[mp + b]);
-                if (b <= a + 2) r0[2 * (size_t)mp + b] = fma(-l2, lb, r0[2 * (size_t)mp + b]);
-                if (b <= a + 3) r0[3 * (size_t)mp + b] = fma(-l3, lb, r0[3 * (size_t)mp + b]);
+    double* wv = colp;                                  // w of the finished pivots (0 for a skipped one)
+    for (int b0 = 0; b0 < m; b0 += 32) {
+        const int b = b0 + lane;
+        const bool bcol = b < m;
+        const int bend = min(b0 + 32, m);
+        if (b0 > 0) {
+            for (int a0 = b0; a0 < m; a0 += 16) {
+                double acc[16];
+#pragma unroll
+                for (int r = 0; r < 16; ++r) { const int a = a0 + r; acc[r] = (bcol && a < m && b <= a) ? g[(size_t)a * mp + b] : 0.0; }
+#pragma unroll 2
+                for (int p = 0; p < b0; ++p) {
+                    const double* Lp = g + (size_t)p * mp;
+                    const double nlb = bcol ? -Lp[b] : 0.0;
+                    const double2* la = reinterpret_cast<const double2*>(Lp + a0);          // a0 is a multiple of 16
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        const double2 v = la[r];
+                        acc[2 * r] = fma(v.x, nlb, acc[2 * r]);
+                        acc[2 * r + 1] = fma(v.y, nlb, acc[2 * r + 1]);
+                    }
+                }
+#pragma unroll
+                for (int r = 0; r < 16; ++r) { const int a = a0 + r; if (bcol && a < m && b <= a) g[(size_t)a * mp + b] = acc[r]; }
             }
-            for (; a < m; ++a) {
-                const double la = colp[a];
-                if (b <= a) g[(size_t)a * mp + b] = fma(-la, lb, g[(size_t)a * mp + b]);
+            if (bcol) {
+                double t = rhs[b];
+                for (int p = 0; p < b0; ++p) t = fma(-g[(size_t)p * mp + b], wv[p], t);
+                rhs[b] = t;
             }
+            __syncwarp();
         }
-        __syncwarp();
+        for (int p = b0; p < bend; ++p) {
+            const double d2 = g[(size_t)p * mp + p], tt = rhs[p], gaa = gd[p];
+            double inv = 0.0, w = 0.0;
+            bool used = true;
+            if (d2 > SSPS_PIVOT_TOL * gaa) { inv = poly_inv_sqrt(d2); w = tt * inv; q = fma(w, w, q); }
+            else if (d2 != d2 || gaa != gaa) { inv = __longlong_as_double(0x7ff8000000000000LL); w = inv; q = inv; }
+            else used = false;                          // numerically dependent column: l_ap = 0 for every a
+            if (lane == 0) wv[p] = w;
+            for (int a = p + 1 + lane; a < m; a += 32) g[(size_t)p * mp + a] = used ? g[(size_t)a * mp + p] * inv : 0.0;
+            __syncwarp();
+            if (used && bcol && b > p) {
+                const double* Lp = g + (size_t)p * mp;
+                const double nlb = -Lp[b];
+                rhs[b] = fma(nlb, w, rhs[b]);
+                int a = b;
+                for (; a + 3 < m; a += 4) {
+                    double* e = g + (size_t)a * mp + b;
+                    const double x0 = fma(Lp[a], nlb, e[0]), x1 = fma(Lp[a + 1], nlb, e[mp]);
+                    const double x2 = fma(Lp[a + 2], nlb, e[2 * (size_t)mp]), x3 = fma(Lp[a + 3], nlb, e[3 * (size_t)mp]);
+                    e[0] = x0; e[mp] = x1; e[2 * (size_t)mp] = x2; e[3 * (size_t)mp] = x3;
+                }
+                for (; a < m; ++a) g[(size_t)a * mp + b] = fma(Lp[a], nlb, g[(size_t)a * mp + b]);
+            }
+            __syncwarp();
+        }
     }
     const double ip = __ldg(P.yty + child) - P.shrink * q;
     return -0.5 * (double)m * P.log1pn - 0.5 * P.dn * log(ip);
@@ -363,14 +420,21 @@ __device__ __noinline__ double poly_score_warp(const SspsDev& P, const PolyDev& 
 // A PC_REFUSE set (more than SSPS_POLY_KW parents whose design is still narrower than n - 1 rows) returns NaN: the callers refuse
 // such sets before they get here.
 __device__ inline double poly_score_any(const SspsDev& P, const PolyDev& Q, const int child, const uint16_t* S, const int k, const bool live,
-                                        const PolyScratch& sc, const PolyWarpScratch& W, const int lane) {
+                                        const PolyScratch& sc, const PolyWarpScratch& W, const int lane, unsigned long long* prof = nullptr) {
     int m = 0;
-    const int cls = live ? poly_class(k, Q.deg, P.n, m) : PC_NONE;
+    const int cls = live ? poly_class(k, Q, P.n, m) : PC_NONE;
     double v = __longlong_as_double(0x7ff8000000000000LL);
+#ifdef SSPS_PROFILE_BIG
+    const long long tq0_ = clock64();
+#endif
     if (cls == PC_EMPTY) v = poly_lml_empty(P, child);
     else if (cls == PC_SAT) v = poly_lml_saturated(P, Q, child, k);
     else if (cls == PC_THREAD) v = poly_score_set(P, Q, child, S, k, m, sc);
     unsigned wm = __ballot_sync(0xffffffffu, cls == PC_WARP);
+#ifdef SSPS_PROFILE_BIG
+    const long long tq1_ = clock64();
+    const unsigned wm0_ = wm;
+#endif
     while (wm) {
         const int src = __ffs(wm) - 1;
         wm &= wm - 1;
@@ -381,6 +445,12 @@ __device__ inline double poly_score_any(const SspsDev& P, const PolyDev& Q, cons
         if (lane == src) v = r;
         __syncwarp();
     }
+#ifdef SSPS_PROFILE_BIG
+    if (prof && lane == 0) {        // warp cycles in the closed-form / THREAD part (its slowest lane) and in the WARP tier; sets scored there
+        atomicAdd(prof + 42, (unsigned long long)(tq1_ - tq0_)); atomicAdd(prof + 43, (unsigned long long)(clock64() - tq1_));
+        atomicAdd(prof + 44, (unsigned long long)__popc(wm0_)); atomicAdd(prof + 45, 1ull);
+    }
+#endif
     return v;
 }
 
@@ -401,11 +471,11 @@ __global__ void __launch_bounds__(128) poly_score_kernel(SspsDev P, PolyDev Q, i
         const int* mem = members + (live ? offsets[s] : 0);
         uint16_t S[SSPS_POLY_KLIST];
         int m = 0;
-        const bool scored = live && k <= SSPS_POLY_KLIST && poly_class(k, Q.deg, P.n, m) != PC_REFUSE;
+        const bool scored = live && k <= SSPS_POLY_KLIST && poly_class(k, Q, P.n, m) != PC_REFUSE;
         if (scored) for (int a = 0; a < k; ++a) S[a] = (uint16_t)mem[a];
         double v = poly_score_any(P, Q, i, S, scored ? k : 0, scored, sc, W, lane);
         if (live && !scored) {      // saturated sets of any size are closed form; anything else this large is refused by the host
-            v = poly_class(k, Q.deg, P.n, m) == PC_SAT ? poly_lml_saturated(P, Q, i, k) : __longlong_as_double(0x7ff8000000000000LL);
+            v = poly_class(k, Q, P.n, m) == PC_SAT ? poly_lml_saturated(P, Q, i, k) : __longlong_as_double(0x7ff8000000000000LL);
         }
         if (live && lml_out) lml_out[s] = v;
         if (live && lp_out) {
@@ -501,7 +571,7 @@ __global__ void __launch_bounds__(128) mh_poly_kernel(const __grid_constant__ Ss
                 }
                 ++s_prop; s_k += (unsigned)kn;
                 int mw = 0;
-                const int cls = poly_class(kn, Q.deg, P.n, mw);
+                const int cls = poly_class(kn, Q, P.n, mw);
                 if (cls == PC_REFUSE) in_range = false;
                 if (in_range && mw > 0) {   // 3 x (n m (m + 5) + m^3/3 + 2 m^2 + 2 m) flops (deg > 1); the host divides by 3
                     const unsigned long long m_ = (unsigned long long)mw;
@@ -509,7 +579,7 @@ __global__ void __launch_bounds__(128) mh_poly_kernel(const __grid_constant__ Ss
                 }
                 if (!in_range) atomicAdd(prm.stats + ST_KCAP_REJECT, 1ull);
             }
-            const double lml_new = poly_score_any(P, Q, i, T, kn, live && in_range, sc, W, lane);
+            const double lml_new = poly_score_any(P, Q, i, T, kn, live && in_range, sc, W, lane, prm.stats);
             if (live) {
                 const bool has_add = action != ACT_REM, has_rem = action != ACT_ADD;
                 double fwd, bwd;

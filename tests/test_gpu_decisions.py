@@ -56,8 +56,13 @@ def test_decisions_verified_at_metric_point():
     with Sampler(large_indeg=15.0, lambda_prop_std=3.0, verify=True, psrf_grid=-1) as s:
         s.set_data(xm, xp, ds.prior_graph)
         st = _verified_run(s, C, n_sweeps, seed=11)
+        raw = s.raw_stats(48)
     assert st.n_proposals == C * V * n_sweeps >= target
     _assert_verified(st, "metric point V=100 n=28")
+    # the BIG tier's removal screening (removal_gain): under verify every screened rejection was re-decided by the exact path and a
+    # disagreement counts as a decision mismatch (asserted 0 above); make sure the run exercised it
+    print("BIG-tier moves with a removal: %d rejected by the screening, %d passed on to the exact path" % (raw[41], raw[40]))
+    assert raw[41] > 10000 and raw[40] > 1000
 
 
 def test_decisions_verified_on_c1(c1):

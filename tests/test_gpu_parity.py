@@ -583,6 +583,47 @@ def test_l1_warp_tier_on_a_well_conditioned_design(oracle, deg):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("deg", [2, 64])
+def test_thread_and_warp_scorers_return_the_same_bits(deg):
+    """ssps_poly.cuh promises that the tier which scores a set (a function of k, deg, n alone) is not visible in the results: one
+    lane's ascending-row fma chain per Gram entry, every Cholesky entry updated in ascending pivot order, in both.  The test hook
+    SSPS_POLY_FORCE_WARP sends the sets of the thread class through the warp-per-set scorer (a second process: the hook is read
+    when the data are set)."""
+    import os, subprocess, sys, tempfile, textwrap
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    d = tempfile.mkdtemp()
+    script = textwrap.dedent("""
+        import sys, numpy as np
+        sys.path.insert(0, %r); sys.path.insert(0, %r)
+        from conftest import make_synth
+        from ssps_b200 import Sampler
+        deg = %d
+        ds, xm, xp = make_synth(30, seed=12, T=31, M=4)
+        rng = np.random.default_rng(5)
+        kmax = {2: 9, 64: 5}[deg]
+        sets = [sorted(rng.choice(30, size=int(rng.integers(1, kmax + 1)), replace=False).tolist()) for _ in range(300)]
+        ch = rng.integers(0, 30, len(sets))
+        with Sampler(regression_deg=deg, large_indeg=15.0, lambda_prop_std=3.0) as s:
+            s.set_data(xm, xp, ds.prior_graph)
+            lml, _ = s.score(ch, sets, np.full(len(sets), 3.0))
+            s.generate(8, seed=2); s.update_loop(30)
+            st = [s.state(c) for c in range(8)]
+        np.savez(sys.argv[1], lml=lml, lam=np.array([x[1] for x in st]), k=np.array([[len(v) for v in x[0]] for x in st]), lml_state=np.array([x[2] for x in st]))
+    """) % (root, os.path.join(root, "tests"), deg)
+    outs = []
+    for force in (False, True):
+        env = dict(os.environ)
+        env.pop("SSPS_POLY_FORCE_WARP", None)
+        if force:
+            env["SSPS_POLY_FORCE_WARP"] = "1"
+        out = os.path.join(d, "f%d.npz" % force)
+        subprocess.check_call([sys.executable, "-c", script, out], env=env)
+        outs.append(np.load(out))
+    for key in ("lml", "lam", "k", "lml_state"):
+        assert np.array_equal(outs[0][key], outs[1][key]), key
+
+
+@pytest.mark.gpu
 def test_l2_replay_interaction_design_warp_tier(oracle):
     """A replayed stream at deg 2 with n = 120 rows and dense starts (large_indeg 10 at V = 20): the chains walk through all
     three scorer classes (k <= 9: thread, 10..14: warp, >= 15: saturated); same decisions as the oracle chain with the QR scorer."""
