@@ -99,10 +99,10 @@ def run_reference(args, rank, world):
     P = orc.Problem(xm, xp, ds.prior_graph, large_indeg=args.large_indeg, lambda_prop_std=args.lambda_prop_std, regression_deg=args.deg)
     cores = os.cpu_count() or 1
     chains = cores
-    # size one step for ~3 s of CPU work
+    # size one step for ~2 s of CPU work (the whole arm, M2 included, has to end within a few minutes at --steps 20 --warmup 5)
     probe = args.cpu_probe_sweeps
     t, nprop, _ = P.run_chains_mt(chains, cores, probe, seed=1, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
-    sweeps = max(probe, int(probe * 3.0 / max(t, 1e-3)))
+    sweeps = max(probe, int(probe * 2.0 / max(t, 1e-3)))
     for w in range(args.warmup):
         P.run_chains_mt(chains, cores, sweeps, seed=2 + w, scorer=orc.SCORER_QR, flags=orc.FLAG_LML_CACHE, want_counts=False)
     tot_t, tot_p = 0.0, 0
@@ -545,10 +545,10 @@ def main():
     ap.add_argument("--psrf-threshold", type=float, default=1.1)
     ap.add_argument("--psrf-check", type=int, default=4000, help="sweeps between convergence checks (multiple of 4)")
     ap.add_argument("--psrf-max-sweeps", type=int, default=3000000)
-    ap.add_argument("--psrf-max-seconds", type=float, default=None, help="default: 90 s on the GPU arm, 240 s on the CPU arm")
+    ap.add_argument("--psrf-max-seconds", type=float, default=None, help="default: 90 s on the GPU arm, 200 s on the CPU arm")
     args = ap.parse_args()
     if args.psrf_max_seconds is None:
-        args.psrf_max_seconds = 240.0 if args.impl == "reference" else 90.0
+        args.psrf_max_seconds = 200.0 if args.impl == "reference" else 90.0
     if args.psrf_seeds is None:
         args.psrf_seeds = 3 if args.impl == "reference" else 5
     preset = {"metric": dict(V=100, T=8, deg="1", chains=4096, sweeps=400, scaling="weak", probe=2000),

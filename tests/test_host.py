@@ -105,3 +105,36 @@ def test_simulator_file_writers(tmp_path):
     series, prior, names = load_formatted_data(str(tmp_path / "ts.tsv"), str(tmp_path / "prior.csv"))
     assert names[0] == "var01" and len(series) == 3
     assert np.array_equal(series[1], ds.series[1]) and np.array_equal(prior, ds.prior_graph)
+
+
+def test_bench_workload_presets(monkeypatch, capsys):
+    """bench.py's presets: the metric point (weak scaling), C4 (1024 chains IN TOTAL: strong scaling splits them over the ranks), C5
+    (regression_deg 'full' = 64); the reference arm cannot exist for C5 and must say so in one JSON line."""
+    import importlib, json, sys
+    bench = importlib.import_module("bench")
+    seen = {}
+
+    def fake_ours(args, rank, world, local_rank):
+        seen["args"] = args
+
+    monkeypatch.setattr(bench, "run_ours", fake_ours)
+    monkeypatch.setattr(bench, "protect_stdout", lambda: None)
+    monkeypatch.setenv("WORLD_SIZE", "1")
+    monkeypatch.setattr(sys, "argv", ["bench.py"])
+    bench.main()
+    a = seen["args"]
+    assert (a.V, a.T, a.deg, a.chains, a.sweeps, a.scaling, a.no_psrf) == (100, 8, 1, 4096, 400, "weak", False)
+    assert a.metric == bench.METRIC
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--workload", "c4"])
+    bench.main()
+    a = seen["args"]
+    assert (a.V, a.T, a.deg, a.chains, a.scaling, a.no_psrf) == (200, 100, 1, 1024, "strong", True) and "V=200" in a.metric
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--workload", "c5"])
+    bench.main()
+    a = seen["args"]
+    assert (a.V, a.T, a.deg, a.deg_label, a.chains, a.scaling, a.no_cpu_baseline) == (1000, 100, 64, "full", 512, "weak", True)
+    capsys.readouterr()
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--workload", "c5", "--impl", "reference"])
+    bench.main()
+    line = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and "unavailable" in line
