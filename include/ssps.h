@@ -77,7 +77,7 @@ typedef struct {
     int32_t struct_size;      /* = sizeof(ssps_config) */
     int32_t device;           /* CUDA ordinal; -1 = current device */
     int32_t regression_deg;   /* --regression-deg (SSPS.jl:75-78).  1: the tabulated-Gram path.  >= 2: interaction columns
-                                 (construct_B), every proposal scored from scratch: one thread per set up to 48 design columns,
+                                 (construct_B), every proposal scored from scratch: one thread per set up to 7 design columns,
                                  the whole warp per set up to n - 2 columns, closed form from n - 1 columns on (any number of
                                  parents); any degree >= max_indegree is Hill's "full" (all non-empty product subsets).
                                  <= 0 (the reference CLI's default -1): the reference builds an EMPTY design -- flat

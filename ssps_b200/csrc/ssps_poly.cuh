@@ -21,10 +21,10 @@
 //              in closed form -- no design is built ("|S| >= n - 1 the projection saturates").  This is what
 //              the reference's rank-cut QR returns for a design of full row rank; it removes every limit on k for
 //              such sets (2^k - 1 >= n - 1 at "full" from k = log2 n on; the reference itself cannot allocate B there).
-//   THREAD     m <= 48, k <= 12: one thread scores one set (poly_score_set): two passes over the n lagged rows (column
+//   THREAD     m <= 7: one thread scores one set (poly_score_set): two passes over the n lagged rows (column
 //              means; Gram matrix of the centred columns and their products with y), scaling to the standardised
 //              design, and the same pivot-skipping Cholesky as the degree-1 path (column order = the reference's).
-//   WARP       48 < m < n - 1 (k <= 64): the whole warp scores one set (poly_score_warp): a lane owns COLUMNS, every
+//   WARP       7 < m < n - 1 (k <= 64): the whole warp scores one set (poly_score_warp): a lane owns COLUMNS, every
 //              Gram entry is accumulated by one lane in ascending row order and the Cholesky is right-looking with every
 //              entry receiving its updates in ascending pivot order -- the operation order of the THREAD tier, so the
 //              two tiers return the same bits and the tier choice (a function of k, deg, n alone) is not visible in
@@ -35,8 +35,11 @@
 #pragma once
 #include "ssps_kernels.cuh"
 
-#define SSPS_POLY_KMAX 12          // THREAD tier: parents per set
-#define SSPS_POLY_MMAX 48          // THREAD tier: design columns per set
+#define SSPS_POLY_KMAX 7           // THREAD tier: parents per set
+#ifndef SSPS_POLY_MMAX
+#define SSPS_POLY_MMAX 7           // THREAD tier: design columns per set (measured on C5: 48 -> 1.17e6, 15 -> 1.49e6, 7 -> 1.56e6 proposals/s:
+                                   // the per-thread Gram accumulators live in global memory, 3 memory operations per fma)
+#endif
 #define SSPS_POLY_KW 64            // WARP tier: parents per set (64-bit column masks)
 #define SSPS_POLY_KLIST 128        // per-thread parent lists of the MH kernel (= the library's hard max_indegree ceiling)
 

@@ -493,14 +493,14 @@ def _poly_class(k, deg, n):
         return "empty", 0
     if m >= n - 1:
         return "sat", m
-    return ("thread" if (m <= 48 and k <= 12) else "warp"), m
+    return ("thread" if m <= 7 else "warp"), m
 
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("deg", [2, 3, 64])
 def test_l1_interaction_design_all_tiers_incl_width_above_n(oracle, deg):
     """The three scorer classes of ssps_poly.cuh against the oracle's pivoted-QR least squares on the explicitly built design
-    (construct_B + `\\`, dbn_distributions.jl:179-248): one thread per set (<= 48 columns), the whole warp per set (49 .. n-2
+    (construct_B + `\\`, dbn_distributions.jl:179-248): one thread per set (<= 7 columns), the whole warp per set (8 .. n-2
     columns), and the closed form for designs of n-1 columns or more (also wider than n: Julia's QR takes any width).
     deg 64 >= |S| is Hill's 'full'.  The closed form is the reference's value whenever its rank-cut QR finds rank n-1; sets
     where it finds less (numerically collinear product columns) are counted and bounded, not asserted to 1e-10."""
