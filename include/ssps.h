@@ -41,6 +41,9 @@
  *        evaluate_convergence / evaluate_summary        scripts/postprocess_samples.jl:155-191
  *   ssps_comm_* / ssps_run_multi / ssps_*_global
  *        pooling of per-chain JSON files                scripts/postprocess_samples.jl:242-259
+ *   ssps_score_static
+ *        no counterpart in the reference: ssps_score on device
+ *        pointers with a fixed in-library scratch array, for callers that cannot allocate
  *
  * Conventions: all indices 0-based (the 1-based <-> 0-based shift lives in the language shim);
  * matrices column-major; the caller owns every buffer passed in or out (inputs are copied to the
@@ -294,6 +297,34 @@ int  ssps_release_cached_memory(int32_t device);
 /* Debug builds only (-DSSPS_BOUNDS: index checks on every scratch / Stage / slot accessor of the kernels): number of failed
  * checks since the library was loaded, on the current device; -1 = the library was built without the checks. */
 int64_t ssps_bounds_failures(void);
+
+/* K2 without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same
+ * scores as ssps_score for regression_deg <= 1 (same device routine, same operation order), with two differences:
+ *   - every array argument is a DEVICE pointer into the caller's own buffers (ssps_score takes host pointers and stages
+ *     them through device blocks it allocates); the results are written there;
+ *   - the per-thread factor scratch comes from ONE file-scope `static __device__` array of
+ *     SSPS_SCORE_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until exit) instead
+ *     of an arena sized per call.  A fixed number of threads walks the sets grid-stride, so n_sets is not limited by it.
+ * The call performs no cudaMalloc / cudaFree (nor any allocating library routine): it validates the sizes, enqueues one
+ * kernel on the handle's stream and RETURNS WITHOUT SYNCHRONISING -- order your own work against that stream
+ * (ssps_set_stream) or synchronise the device.  The first call on a device resolves the array's device address
+ * (cudaGetSymbolAddress); make it once before a graph capture begins.
+ * Limits (beyond them: SSPS_ERR_INVALID and a message, nothing is launched): 0 <= max_parents <=
+ * SSPS_SCORE_STATIC_MAX_PARENTS, 0 <= n_sets <= SSPS_SCORE_STATIC_MAX_SETS.  max_parents is the caller's bound on the
+ * set sizes (the host cannot read device offsets without a copy): a set with more members than that, a child or member
+ * outside [0, V), or members not strictly ascending gets NaN in every requested output -- checked on the device.
+ * regression_deg >= 2 handles: SSPS_ERR_UNSUPPORTED (their scratch is orders of magnitude larger).
+ * All calls in a process share the array per device: two calls that overlap on the GPU (different streams, different
+ * handles, different host threads) RACE on it -- serialise them on one stream.  The array keeps the last call's contents;
+ * nothing in it has to start at zero (every factor row, w entry and id is written before it is read within one set), so
+ * nothing is cleared.  d_lambda may be NULL iff d_logprior_out is NULL; any output may be NULL. */
+#define SSPS_SCORE_STATIC_MAX_PARENTS   64
+#define SSPS_SCORE_STATIC_MAX_SETS      (1 << 24)
+#define SSPS_SCORE_STATIC_SCRATCH_BYTES (16u << 20)
+int  ssps_score_static(ssps_handle* h, int32_t n_sets, int32_t max_parents,
+                       const int32_t* d_child, const int32_t* d_set_offsets /* n_sets + 1 */, const int32_t* d_set_members,
+                       const double* d_lambda, double* d_lml_out, double* d_logprior_out, double* d_min_pivot_out);
 
 #ifdef __cplusplus
 }

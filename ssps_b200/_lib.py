@@ -93,6 +93,8 @@ SIGNATURES = {
     "ssps_measure_gather_peak": (C.c_int, [_hp, C.c_int64, _dp, _dp, _dp]),
     "ssps_release_cached_memory": (C.c_int, [C.c_int32]),
     "ssps_bounds_failures": (C.c_int64, []),
+    # device pointers (plain addresses): the call allocates nothing and stages nothing
+    "ssps_score_static": (C.c_int, [_hp, C.c_int32, C.c_int32] + [C.c_void_p] * 7),
 }
 
 _lib = None

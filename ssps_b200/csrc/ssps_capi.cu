@@ -2064,3 +2064,119 @@ int ssps_convergence(ssps_handle* const* hs, int32_t n, double burnin, int64_t l
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// K2 without allocation (ssps_score_static).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (graph capture, serving loops).  The per-thread factor scratch of
+// the scorer lives in ONE file-scope device array of a fixed size; everything else is the caller's device memory.
+// ================================================================================================
+namespace {
+
+// Held by every GPU that loads the library until the process exits.  Shared by all calls on a device: calls that
+// overlap on the GPU race on it (ssps.h).  Keeps the last call's contents; score_set writes every element before it
+// reads it (row a of the factor, w(a), the ids), so nothing has to start at zero.
+static __device__ __align__(256) unsigned char g_score_static_scratch[SSPS_SCORE_STATIC_SCRATCH_BYTES];
+
+// In host code the name above is a host-side stand-in, not a device address: the address the kernel gets comes from
+// cudaGetSymbolAddress, once per device, with that device current.  Fixed table: no host allocation either.
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kStaticMaxDevices] = {};
+
+int static_scratch_ptr(int device, unsigned char** out) {
+    if (device < 0 || device >= kStaticMaxDevices) return fail(SSPS_ERR_UNSUPPORTED, "ssps_score_static: device %d beyond the table of %d", device, kStaticMaxDevices);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[device]) {
+        int cur = -1;
+        CK(cudaGetDevice(&cur));
+        if (cur != device) return fail(SSPS_ERR_CUDA, "ssps_score_static: device %d is current, the handle lives on %d", cur, device);
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_score_static_scratch);
+        if (e != cudaSuccess || !p) return fail(SSPS_ERR_CUDA, "cudaGetSymbolAddress(g_score_static_scratch): %s", cudaGetErrorString(e));
+        g_static_ptr[device] = p;
+    }
+    *out = (unsigned char*)g_static_ptr[device];
+    return SSPS_OK;
+}
+
+// bytes of scratch one thread needs for sets of at most kcap parents: factor rows + w (fp64), ids (uint16)
+inline size_t static_bytes_per_thread(int kcap) { return (size_t)(SSPS_TRI(kcap) + kcap) * sizeof(double) + (size_t)kcap * sizeof(uint16_t); }
+
+// A fixed number of threads walks the sets grid-stride; thread t owns column t of the interleaved scratch (element e at
+// [e * stride + t], the layout of score_kernel's arena).  The sets come from device memory the host has not seen, so
+// the checks ssps_score makes on the host are made here: an invalid set gets NaN, the scratch is never indexed by it.
+__global__ void score_static_kernel(SspsDev P, int n_sets, int kcap, const int* __restrict__ child, const int* __restrict__ offsets,
+                                    const int* __restrict__ members, const double* __restrict__ lambda,
+                                    double* __restrict__ arena_d, uint16_t* __restrict__ arena_t,
+                                    double* __restrict__ lml_out, double* __restrict__ lp_out, double* __restrict__ minp_out) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int stride = gridDim.x * blockDim.x;
+    Scratch sc{arena_d + tid, arena_t + tid, stride, kcap};
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    for (int s = tid; s < n_sets; s += stride) {
+        const int i = child[s];
+        const long long o0 = offsets[s], o1 = offsets[s + 1];
+        const long long kk = o1 - o0;
+        bool ok = i >= 0 && i < P.V && o0 >= 0 && kk >= 0 && kk <= (long long)kcap;
+        const int k = ok ? (int)kk : 0;
+        const int* mem = members + (ok ? o0 : 0);
+        for (int a = 0; a < k; ++a) {
+            const int j = mem[a];
+            if (j < 0 || j >= P.V || (a > 0 && j <= mem[a - 1])) { ok = false; break; }
+            sc.T(a) = (uint16_t)j;
+        }
+        if (!ok) {
+            if (lml_out) lml_out[s] = nan;
+            if (minp_out) minp_out[s] = nan;
+            if (lp_out) lp_out[s] = nan;
+            continue;
+        }
+        double minr;
+        const double lml = score_set(P, i, sc, k, &minr);
+        if (lml_out) lml_out[s] = lml;
+        if (minp_out) minp_out[s] = minr;
+        if (lp_out) {
+            const double lam = lambda[s];
+            double somc = 0.0;
+            for (int a = 0; a < k; ++a) somc += P.omc[(size_t)mem[a] + (size_t)P.V * i];
+            lp_out[s] = -lam * somc - prior_normaliser(P, i, lam);
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int ssps_score_static(ssps_handle* h, int32_t n_sets, int32_t max_parents, const int32_t* d_child, const int32_t* d_set_offsets,
+                      const int32_t* d_set_members, const double* d_lambda, double* d_lml_out, double* d_logprior_out,
+                      double* d_min_pivot_out) {
+    CKS(bind(h));
+    if (!h->has_data) return fail(SSPS_ERR_INVALID, "ssps_score_static before ssps_set_data");
+    if (h->is_poly) return fail(SSPS_ERR_UNSUPPORTED, "ssps_score_static: regression_deg=%d scores every set from scratch and needs far more scratch "
+                                "than the fixed array of %u bytes; use ssps_score", h->cfg.regression_deg, (unsigned)SSPS_SCORE_STATIC_SCRATCH_BYTES);
+    if (n_sets < 0 || n_sets > SSPS_SCORE_STATIC_MAX_SETS)
+        return fail(SSPS_ERR_INVALID, "ssps_score_static: n_sets=%d outside [0, %d]", n_sets, (int)SSPS_SCORE_STATIC_MAX_SETS);
+    if (max_parents < 0 || max_parents > SSPS_SCORE_STATIC_MAX_PARENTS)
+        return fail(SSPS_ERR_INVALID, "ssps_score_static: max_parents=%d outside [0, %d] (the fixed scratch array of %u bytes is sized for that; "
+                    "use ssps_score for larger sets)", max_parents, (int)SSPS_SCORE_STATIC_MAX_PARENTS, (unsigned)SSPS_SCORE_STATIC_SCRATCH_BYTES);
+    if (n_sets > 0 && (!d_child || !d_set_offsets || (max_parents > 0 && !d_set_members))) return fail(SSPS_ERR_INVALID, "ssps_score_static: null input");
+    if (d_logprior_out && !d_lambda) return fail(SSPS_ERR_INVALID, "ssps_score_static: d_logprior_out needs d_lambda");
+    unsigned char* base = nullptr;
+    CKS(static_scratch_ptr(h->device, &base));          // also on an empty batch: the warm-up call before a graph capture
+    if (n_sets == 0) return SSPS_OK;
+    const int kcap = std::max(max_parents, 1);
+    const int block = 128;
+    const size_t per_thread = static_bytes_per_thread(kcap);
+    const size_t fit = (size_t)SSPS_SCORE_STATIC_SCRATCH_BYTES / per_thread / block;         // CTAs the array has room for
+    if (fit < 1) return fail(SSPS_ERR_UNSUPPORTED, "ssps_score_static: scratch array too small for one CTA at max_parents=%d", max_parents);
+    const int grid = (int)std::min<size_t>(std::min<size_t>(fit, (size_t)div_up((size_t)n_sets, block)), (size_t)h->sm_count * 8);
+    const size_t nthreads = (size_t)grid * block;
+    double* arena_d = (double*)base;                                                          // 256-byte aligned
+    uint16_t* arena_t = (uint16_t*)(base + nthreads * (size_t)(SSPS_TRI(kcap) + kcap) * sizeof(double));
+    score_static_kernel<<<grid, block, 0, h->stream>>>(h->dev, n_sets, kcap, d_child, d_set_offsets, d_set_members, d_lambda, arena_d, arena_t,
+                                                       d_lml_out, d_logprior_out, d_min_pivot_out);
+    return launch_ok(h, "score_static_kernel");
+}
+
+}  // extern "C"

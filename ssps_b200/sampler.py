@@ -167,6 +167,16 @@ class Sampler:
         check(self._L.ssps_score(self._h, ns, _i(ch), _i(offs), _i(mem), _d(lam), _d(lml), _d(lp), _d(mp)))
         return (lml, lp, mp) if want_min_pivot else (lml, lp)
 
+    def score_static(self, n_sets: int, max_parents: int, d_child: int, d_set_offsets: int, d_set_members: int,
+                     d_lambda: Optional[int] = None, d_lml_out: Optional[int] = None, d_logprior_out: Optional[int] = None,
+                     d_min_pivot_out: Optional[int] = None) -> None:
+        """ssps_score_static: the scores of score() from DEVICE buffers of the caller (addresses as ints; int32 CSR, fp64
+        outputs), the factor scratch from a fixed array inside the library: no allocation anywhere in the call.  Enqueued on
+        the sampler's stream and NOT synchronised; at most 64 parents per set (include/ssps.h).  No counterpart in the
+        reference (added for callers that cannot call cudaMalloc)."""
+        check(self._L.ssps_score_static(self._h, n_sets, max_parents, d_child, d_set_offsets, d_set_members, d_lambda, d_lml_out,
+                                        d_logprior_out, d_min_pivot_out))
+
     def log_marg_lik(self, ind: int, parent_inds: Sequence[int]) -> float:
         return float(self.score([ind], [sorted(parent_inds)])[0][0])
 
